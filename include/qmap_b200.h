@@ -1,0 +1,348 @@
+/*
+ * qmap_b200.h - C ABI of the B200-native heuristic router.
+ *
+ * One hot path of cda-tum/mqt-qmap is rebuilt behind this boundary: the
+ * superconducting heuristic mapper's cost tables and its per-layer A* SWAP
+ * search.  Every entry point names the reference interface it replaces
+ * (paths relative to the reference tree).  Plain pointers and sizes only; the
+ * caller owns every host buffer, the library owns device memory behind the
+ * opaque handles.  No exception crosses this boundary: every function returns
+ * a qmg_status and qmg_last_error() holds the message (thread-local).
+ *
+ * There is no CPU fallback: without a CUDA device every compute entry point
+ * returns QMG_NO_DEVICE.
+ */
+#ifndef QMAP_B200_H
+#define QMAP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  QMG_OK = 0,
+  /* HeuristicMapper.cpp:637-639 "No viable mapping found." */
+  QMG_NO_VIABLE_MAPPING = 1,
+  /* HeuristicMapper.cpp:563 automatic layer split requested by the search */
+  QMG_SPLIT_LIMIT_HIT = 2,
+  QMG_BAD_ARG = 3,
+  QMG_CUDA_ERROR = 4,
+  QMG_OOM = 5,
+  /* the per-instance node pool is full (raise qmg_route_options.pool_nodes) */
+  QMG_POOL_EXHAUSTED = 6,
+  QMG_NO_DEVICE = 7
+} qmg_status;
+
+/* include/sc/configuration/Heuristic.hpp:17-36 (same order) */
+typedef enum {
+  QMG_HEUR_GATE_COUNT_MAX_DISTANCE = 0,
+  QMG_HEUR_GATE_COUNT_SUM_DISTANCE = 1,
+  QMG_HEUR_GATE_COUNT_SUM_DISTANCE_MINUS_SHARED_SWAPS = 2,
+  QMG_HEUR_GATE_COUNT_MAX_DISTANCE_OR_SUM_DISTANCE_MINUS_SHARED_SWAPS = 3,
+  QMG_HEUR_FIDELITY_BEST_LOCATION = 4
+} qmg_heuristic;
+
+/* include/sc/configuration/LookaheadHeuristic.hpp:17-25 */
+typedef enum {
+  QMG_LOOKAHEAD_NONE = 0,
+  QMG_LOOKAHEAD_GATE_COUNT_MAX_DISTANCE = 1,
+  QMG_LOOKAHEAD_GATE_COUNT_SUM_DISTANCE = 2
+} qmg_lookahead;
+
+/* include/sc/configuration/EarlyTermination.hpp:17-24 */
+typedef enum {
+  QMG_ET_NONE = 0,
+  QMG_ET_EXPANDED_NODES = 1,
+  QMG_ET_EXPANDED_NODES_AFTER_FIRST_SOLUTION = 2,
+  QMG_ET_EXPANDED_NODES_AFTER_CURRENT_OPTIMAL_SOLUTION = 3,
+  QMG_ET_SOLUTION_NODES = 4,
+  QMG_ET_SOLUTION_NODES_AFTER_CURRENT_OPTIMAL_SOLUTION = 5
+} qmg_early_termination;
+
+/* include/sc/configuration/Layering.hpp:17-23 */
+typedef enum {
+  QMG_LAYERING_INDIVIDUAL_GATES = 0,
+  QMG_LAYERING_DISJOINT_QUBITS = 1,
+  QMG_LAYERING_ODD_GATES = 2,
+  QMG_LAYERING_QUBIT_TRIANGLE = 3,
+  QMG_LAYERING_DISJOINT_2Q_BLOCKS = 4
+} qmg_layering;
+
+/* include/sc/configuration/InitialLayout.hpp:20 */
+typedef enum {
+  QMG_LAYOUT_IDENTITY = 0,
+  QMG_LAYOUT_STATIC = 1,
+  QMG_LAYOUT_DYNAMIC = 2
+} qmg_initial_layout;
+
+/*
+ * POD mirror of the fields of Configuration (include/sc/configuration/
+ * Configuration.hpp:30-119) the heuristic path reads.  Defaults are the
+ * reference's (qmg_config_default()).
+ */
+typedef struct {
+  int32_t heuristic;           /* qmg_heuristic */
+  int32_t lookahead_heuristic; /* qmg_lookahead */
+  uint32_t nr_lookaheads;
+  uint32_t _pad0;
+  double first_lookahead_factor;
+  double lookahead_factor;
+  int32_t early_termination; /* qmg_early_termination */
+  int32_t automatic_layer_splits;
+  uint64_t early_termination_limit;
+  uint64_t automatic_layer_splits_node_limit;
+  /* host-side fields (layering / placement / emission) */
+  int32_t layering;       /* qmg_layering */
+  int32_t initial_layout; /* qmg_initial_layout */
+  uint32_t iterative_bidirectional_routing_passes;
+  int32_t swap_on_first_layer;
+  int32_t add_barriers_between_layers;
+  int32_t add_measurements_to_mapped_circuit;
+  int32_t pre_mapping_optimizations;
+  int32_t post_mapping_optimizations;
+  int32_t debug;
+  int32_t verbose;
+} qmg_config;
+
+void qmg_config_default(qmg_config* cfg);
+
+/* ------------------------------------------------------------------------ */
+/* Cost tables                                                              */
+/* ------------------------------------------------------------------------ */
+
+/*
+ * Stand-alone table kernels.  Matrices are dense row-major n*n doubles, the
+ * coupling map is nEdges directed (first, second) pairs in ascending
+ * lexicographic order (the iteration order of the reference's
+ * std::set<std::pair<uint16_t,uint16_t>>, include/sc/utils.hpp:27-29).
+ */
+
+/* Dijkstra::buildTable (src/sc/utils.cpp:26-54): all-pairs cheapest path over
+ * the undirected view of the coupling map with directed weights
+ * edgeWeights[from*n+to]; diagonal 0, unreachable -1.
+ * exact_association != 0 reproduces the reference's left-to-right
+ * floating-point path sums bit for bit (label-correcting kernel); 0 uses the
+ * blocked min-plus Floyd-Warshall kernel (bit-exact for integer weights,
+ * <= 1e-9 relative otherwise). */
+int qmg_build_table(uint16_t n, const uint16_t* edges, size_t nEdges,
+                    const double* edgeWeights, int exact_association,
+                    double* distanceTable, int device);
+
+/* Dijkstra::buildSingleEdgeSkipTable (src/sc/utils.cpp:147-183) */
+int qmg_build_single_edge_skip_table(uint16_t n, const double* distanceTable,
+                                     const uint16_t* edges, size_t nEdges,
+                                     double reversalCost,
+                                     double* edgeSkipDistanceTable, int device);
+
+/* Dijkstra::buildEdgeSkipTable (src/sc/utils.cpp:91-145).  tables receives up
+ * to maxTables matrices of n*n doubles; *nTables is the number produced (the
+ * reference stops at the first all-zero table and drops it). */
+int qmg_build_edge_skip_table(uint16_t n, const uint16_t* edges, size_t nEdges,
+                              const double* edgeWeights, int exact_association,
+                              double* tables, size_t maxTables,
+                              size_t* nTables, int device);
+
+/*
+ * Architecture handle: the device-resident form of class Architecture
+ * (include/sc/Architecture.hpp:42).  qmg_arch_create replaces
+ * Architecture::createDistanceTable (src/sc/Architecture.cpp:201-230);
+ * qmg_arch_set_fidelity_costs replaces the table part of
+ * Architecture::createFidelityTable (src/sc/Architecture.cpp:232-294): the
+ * caller computes the -log2 cost vectors on the host exactly as the reference
+ * does (:248-289) and passes them in; the k-edge-skip tables are built on the
+ * device.
+ */
+typedef struct qmg_arch qmg_arch;
+
+int qmg_arch_create(uint16_t n, const uint16_t* edges, size_t nEdges,
+                    int device, qmg_arch** out);
+int qmg_arch_set_fidelity_costs(qmg_arch* arch,
+                                const double* singleQubitFidelityCosts /* n */,
+                                const double* twoQubitFidelityCosts /* n*n */,
+                                const double* swapFidelityCosts /* n*n */);
+void qmg_arch_destroy(qmg_arch* arch);
+
+typedef struct {
+  uint16_t n;
+  uint16_t _pad;
+  uint32_t n_edges;
+  int32_t bidirectional;  /* Architecture::bidirectional() */
+  int32_t unidirectional; /* Architecture::unidirectional() */
+  int32_t fidelity_available;
+  uint32_t n_fidelity_tables; /* getFidelityDistanceTables().size() */
+  int32_t device;
+  float table_build_ms; /* device time spent building the tables */
+} qmg_arch_info;
+
+int qmg_arch_get_info(const qmg_arch* arch, qmg_arch_info* info);
+/* getDistanceTable(includeReversalCost) (include/sc/Architecture.hpp:258) */
+int qmg_arch_get_distance_table(const qmg_arch* arch, int includeReversalCost,
+                                double* out /* n*n */);
+/* getFidelityDistanceTables() (include/sc/Architecture.hpp:283) */
+int qmg_arch_get_fidelity_distance_tables(const qmg_arch* arch,
+                                          double* out /* K*n*n */);
+
+/* ------------------------------------------------------------------------ */
+/* A* routing                                                               */
+/* ------------------------------------------------------------------------ */
+
+/* one entry of TwoQubitMultiplicity (include/sc/Mapper.hpp:33-34): logical
+ * pair q1 < q2 with the number of gates q1->q2 (forward) and q2->q1. */
+typedef struct {
+  uint16_t q1, q2, forward, reverse;
+} qmg_gate2q;
+
+/* one non-zero entry of SingleQubitMultiplicity (include/sc/Mapper.hpp:36) */
+typedef struct {
+  uint16_t qubit, multiplicity;
+} qmg_gate1q;
+
+/*
+ * The layers of one circuit as produced by Mapper::createLayers
+ * (src/sc/Mapper.cpp:138-281), flattened to CSR.  Gates of a layer are in
+ * std::map<Edge,...> order (ascending (q1,q2)); 1q entries ascending qubit.
+ */
+typedef struct {
+  uint32_t n_layers;
+  uint32_t n_logical; /* logical qubit indices are < n_logical <= n */
+  const uint32_t* gate2q_offsets; /* n_layers+1 */
+  const qmg_gate2q* gates2q;
+  const uint32_t* gate1q_offsets; /* n_layers+1 */
+  const qmg_gate1q* gates1q;
+} qmg_layers;
+
+/* one search unit: a circuit, a start layout and a pass schedule */
+typedef struct {
+  qmg_layers layers;
+  /* start layout: locations[logical] = physical or -1 (Mapper::locations);
+   * n entries.  NULL = all unplaced (InitialLayout::Dynamic). */
+  const int16_t* initial_locations;
+  /* number of forward+backward pseudo-routing passes before the final
+   * routing pass (Configuration::iterativeBidirectionalRoutingPasses,
+   * HeuristicMapper.cpp:74-89) */
+  uint32_t bidirectional_passes;
+  /* first layer of the final pass to route and number of layers to route
+   * (n_route_layers = 0 means "to the end"); used to resume after a split */
+  uint32_t first_layer;
+  uint32_t n_route_layers;
+  uint32_t _pad;
+} qmg_instance;
+
+/* result of one aStarMap call (HeuristicMapper::Node + the counters of
+ * MappingResults::LayerHeuristicBenchmarkInfo, include/sc/MappingResults.hpp:
+ * 62-93) */
+typedef struct {
+  double cost_fixed;
+  double cost_fixed_reversals;
+  double cost_heur;
+  double lookahead_penalty;
+  uint64_t expanded_nodes;
+  uint64_t generated_nodes;
+  uint64_t expanded_nodes_after_first_solution;
+  uint64_t expanded_nodes_after_optimal_solution;
+  uint64_t solution_nodes;
+  uint64_t solution_nodes_after_optimal_solution;
+  uint64_t layout_hash; /* FNV-1a over the result's qubits[] */
+  uint32_t solution_depth;
+  uint32_t result_node_id;
+  uint32_t swap_offset; /* into qmg_route_result.swaps */
+  uint32_t n_swaps;
+  uint32_t placement_offset; /* into qmg_route_result.placements */
+  uint32_t n_placements;
+  int32_t early_termination;
+  int32_t status; /* qmg_status of this layer */
+} qmg_layer_result;
+
+/* a logical qubit placed by mapUnmappedGates (HeuristicMapper.cpp:211-307) */
+typedef struct {
+  uint16_t logical, physical;
+} qmg_placement;
+
+/*
+ * Caller-allocated output of one instance.  Capacities are in elements; the
+ * library fails with QMG_BAD_ARG rather than overrun them.
+ */
+typedef struct {
+  qmg_layer_result* layers; /* capacity n_layers of the instance */
+  uint16_t* swaps;          /* pairs (first, second); capacity swap_capacity */
+  uint32_t swap_capacity;
+  uint32_t n_swaps_total;
+  qmg_placement* placements; /* capacity n (each logical placed once) */
+  uint32_t placement_capacity;
+  uint32_t n_placements_total;
+  int16_t* final_qubits;    /* n: Mapper::qubits after the last layer */
+  int16_t* final_locations; /* n: Mapper::locations after the last layer */
+  /* layout before the final routing pass (after pseudo-routing passes) */
+  int16_t* start_locations; /* n or NULL */
+  /* optional: qubits[] after every layer of the final pass, n_layers*n */
+  int16_t* layer_qubits;
+  uint32_t n_layers_done; /* layers of the final pass completed */
+  int32_t status;         /* QMG_OK, or the status that stopped the instance;
+                             on QMG_SPLIT_LIMIT_HIT n_layers_done is the layer
+                             to split and final_* hold the layout before it */
+  uint64_t expanded_nodes;  /* all passes, incl. pseudo-routing */
+  uint64_t generated_nodes; /* all passes */
+} qmg_route_result;
+
+typedef struct {
+  uint32_t pool_nodes;       /* node-pool capacity per resident search, 0=auto */
+  uint32_t threads_per_search; /* 32..256, 0 = auto from n */
+  uint32_t searches_per_sm;  /* resident searches per SM, 0 = auto */
+  uint32_t _pad;
+} qmg_route_options;
+
+typedef struct {
+  float kernel_ms;   /* device time of the routing kernel (CUDA events) */
+  float h2d_ms;      /* staging */
+  float d2h_ms;
+  uint32_t grid;     /* CTAs launched */
+  uint32_t block;    /* threads per CTA */
+  uint64_t h2d_bytes;
+  uint64_t d2h_bytes;
+  uint64_t expanded_nodes; /* sum over instances and passes */
+  uint64_t generated_nodes;
+  uint32_t kernel_launches;
+  uint32_t _pad;
+} qmg_route_stats;
+
+/*
+ * Route a batch of independent instances on one device.  For every instance
+ * this runs what HeuristicMapper::map does between createInitialMapping and
+ * postMappingOptimizations (HeuristicMapper.cpp:74-91): the pseudo-routing
+ * passes and the final routing pass, i.e. for each layer mapUnmappedGates
+ * (:211-307) followed by the A* search of aStarMap (:521-696) with expandNode
+ * (:698-748), applySWAP (:861-973), the heuristics (:1055-1354) and the
+ * lookahead penalties (:1356-1513), on an open list with the semantics of
+ * UniquePriorityQueue (include/sc/heuristic/UniquePriorityQueue.hpp:59-93).
+ */
+int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
+                    size_t nInstances, const qmg_instance* instances,
+                    qmg_route_result* results,
+                    const qmg_route_options* options /* NULL = auto */,
+                    qmg_route_stats* stats /* NULL = none */);
+
+/*
+ * Device-resident variant: stage a batch once, then run it repeatedly with
+ * the inputs already in HBM (used to separate kernel time from staging).
+ */
+typedef struct qmg_batch qmg_batch;
+int qmg_batch_create(const qmg_arch* arch, const qmg_config* cfg,
+                     size_t nInstances, const qmg_instance* instances,
+                     const qmg_route_options* options, qmg_batch** out);
+int qmg_batch_run(qmg_batch* batch, qmg_route_stats* stats);
+int qmg_batch_fetch(qmg_batch* batch, qmg_route_result* results);
+void qmg_batch_destroy(qmg_batch* batch);
+
+/* message of the last failing call on this thread ("" if none) */
+const char* qmg_last_error(void);
+/* number of visible CUDA devices (0 without a driver) */
+int qmg_device_count(void);
+const char* qmg_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QMAP_B200_H */

@@ -1,0 +1,247 @@
+// Stand-in for mqt-core's qc::QuantumComputation: a gate list plus the layout
+// bookkeeping (initialLayout, outputPermutation, ancillary/garbage flags) the
+// reference's Mapper/HeuristicMapper touch. TEST INFRASTRUCTURE (oracle/_ref
+// build only). Semantics that matter for parity are noted inline.
+#pragma once
+#include "ir/Definitions.hpp"
+#include "ir/Permutation.hpp"
+#include "ir/operations/CompoundOperation.hpp"
+#include "ir/operations/StandardOperation.hpp"
+#include <algorithm>
+#include <fstream>
+#include <memory>
+#include <optional>
+#include <ostream>
+#include <string>
+#include <vector>
+
+namespace qc {
+class QuantumComputation {
+public:
+  using Ops = std::vector<std::unique_ptr<Operation>>;
+
+protected:
+  Ops ops;
+  std::size_t nqubits = 0;
+  std::size_t nancillae = 0;
+  std::size_t nclassics = 0;
+  std::string name;
+  QuantumRegisterMap qregs;
+  QuantumRegisterMap ancregs;
+  ClassicalRegisterMap cregs;
+  std::vector<bool> ancillary;
+  std::vector<bool> garbage;
+
+public:
+  Permutation initialLayout;
+  Permutation outputPermutation;
+
+  QuantumComputation() = default;
+  explicit QuantumComputation(std::size_t nq, std::size_t nc = 0) {
+    if (nq > 0) {
+      addQubitRegister(nq);
+    }
+    if (nc > 0) {
+      addClassicalRegister(nc);
+    }
+  }
+  QuantumComputation(const QuantumComputation& o)
+      : nqubits(o.nqubits), nancillae(o.nancillae), nclassics(o.nclassics),
+        name(o.name), qregs(o.qregs), ancregs(o.ancregs), cregs(o.cregs),
+        ancillary(o.ancillary), garbage(o.garbage),
+        initialLayout(o.initialLayout),
+        outputPermutation(o.outputPermutation) {
+    ops.reserve(o.ops.size());
+    for (const auto& op : o.ops) {
+      ops.emplace_back(op->clone());
+    }
+  }
+  QuantumComputation(QuantumComputation&&) noexcept = default;
+  QuantumComputation& operator=(const QuantumComputation& o) {
+    if (this != &o) {
+      QuantumComputation tmp(o);
+      *this = std::move(tmp);
+    }
+    return *this;
+  }
+  QuantumComputation& operator=(QuantumComputation&&) noexcept = default;
+
+  [[nodiscard]] std::size_t getNqubits() const { return nqubits + nancillae; }
+  [[nodiscard]] std::size_t getNancillae() const { return nancillae; }
+  [[nodiscard]] std::size_t getNops() const { return ops.size(); }
+  [[nodiscard]] const std::string& getName() const { return name; }
+  void setName(const std::string& n) { name = n; }
+  [[nodiscard]] const QuantumRegisterMap& getQuantumRegisters() const {
+    return qregs;
+  }
+  [[nodiscard]] const QuantumRegisterMap& getAncillaRegisters() const {
+    return ancregs;
+  }
+  [[nodiscard]] const ClassicalRegisterMap& getClassicalRegisters() const {
+    return cregs;
+  }
+
+  void addQubitRegister(std::size_t nq, const std::string& regName = "q") {
+    const auto start = static_cast<Qubit>(nqubits + nancillae);
+    qregs[regName] = QuantumRegister(start, nq, regName);
+    for (std::size_t i = 0; i < nq; ++i) {
+      const auto j = static_cast<Qubit>(start + i);
+      initialLayout[j] = j;
+      outputPermutation[j] = j;
+    }
+    nqubits += nq;
+    ancillary.resize(nqubits + nancillae, false);
+    garbage.resize(nqubits + nancillae, false);
+  }
+  void addClassicalRegister(std::size_t nc, const std::string& regName = "c") {
+    cregs[regName] = ClassicalRegister(nclassics, nc, regName);
+    nclassics += nc;
+  }
+  void addAncillaryQubit(Qubit physical, std::optional<Qubit> output) {
+    const auto logical = static_cast<Qubit>(nqubits + nancillae);
+    ++nancillae;
+    ancillary.resize(nqubits + nancillae, false);
+    garbage.resize(nqubits + nancillae, false);
+    ancillary[logical] = true;
+    initialLayout[physical] = logical;
+    if (output.has_value()) {
+      outputPermutation[physical] = *output;
+    } else {
+      garbage[logical] = true;
+    }
+  }
+  void setLogicalQubitAncillary(Qubit logical) {
+    if (logical >= ancillary.size()) {
+      ancillary.resize(logical + 1U, false);
+    }
+    ancillary[logical] = true;
+  }
+  // marking a logical qubit garbage also drops it from the output permutation
+  void setLogicalQubitGarbage(Qubit logical) {
+    if (logical >= garbage.size()) {
+      garbage.resize(logical + 1U, false);
+    }
+    garbage[logical] = true;
+    for (auto it = outputPermutation.begin(); it != outputPermutation.end();
+         ++it) {
+      if (it->second == logical) {
+        outputPermutation.erase(it);
+        break;
+      }
+    }
+  }
+  [[nodiscard]] bool logicalQubitIsGarbage(Qubit l) const {
+    return l < garbage.size() && garbage[l];
+  }
+  [[nodiscard]] bool isIdleQubit(Qubit physical) const {
+    return std::none_of(ops.begin(), ops.end(), [physical](const auto& op) {
+      return op->actsOn(physical);
+    });
+  }
+  // Idle qubits are dropped from both layout maps and from the qubit count;
+  // the remaining qubits keep their indices (this is what the reference's
+  // golden layout {0,1,2,-1,4} for 4gt11_84 shows, test_heuristic.cpp:431).
+  void stripIdleQubits(bool force = false) {
+    auto layoutCopy = initialLayout;
+    for (auto it = layoutCopy.rbegin(); it != layoutCopy.rend(); ++it) {
+      const auto physical = it->first;
+      if (!isIdleQubit(physical)) {
+        continue;
+      }
+      if (!force && outputPermutation.count(physical) > 0) {
+        continue;
+      }
+      initialLayout.erase(physical);
+      outputPermutation.erase(physical);
+      if (nqubits > 0) {
+        --nqubits;
+      }
+    }
+  }
+  void unifyQuantumRegisters(const std::string& regName = "q") {
+    qregs.clear();
+    ancregs.clear();
+    nqubits += nancillae;
+    nancillae = 0;
+    qregs[regName] = QuantumRegister(0, nqubits, regName);
+  }
+  void appendMeasurementsAccordingToOutputPermutation(
+      const std::string& regName = "c") {
+    if (nclassics < outputPermutation.size()) {
+      addClassicalRegister(outputPermutation.size() - nclassics, regName);
+    }
+    for (const auto& [physical, logical] : outputPermutation) {
+      ops.emplace_back(std::make_unique<NonUnitaryOperation>(
+          Targets{physical}, std::vector<Bit>{logical}));
+    }
+  }
+  void reset() {
+    ops.clear();
+    nqubits = nancillae = nclassics = 0;
+    qregs.clear();
+    ancregs.clear();
+    cregs.clear();
+    initialLayout.clear();
+    outputPermutation.clear();
+    ancillary.clear();
+    garbage.clear();
+  }
+
+  // gate list access
+  [[nodiscard]] auto begin() { return ops.begin(); }
+  [[nodiscard]] auto end() { return ops.end(); }
+  [[nodiscard]] auto begin() const { return ops.begin(); }
+  [[nodiscard]] auto end() const { return ops.end(); }
+  [[nodiscard]] auto cbegin() const { return ops.cbegin(); }
+  [[nodiscard]] auto cend() const { return ops.cend(); }
+  [[nodiscard]] auto rbegin() { return ops.rbegin(); }
+  [[nodiscard]] auto rend() { return ops.rend(); }
+  [[nodiscard]] bool empty() const { return ops.empty(); }
+  [[nodiscard]] std::size_t size() const { return ops.size(); }
+  auto erase(Ops::const_iterator it) { return ops.erase(it); }
+  void pop_back() { ops.pop_back(); }
+  [[nodiscard]] const auto& back() const { return ops.back(); }
+
+  template <class T, class... Args> void emplace_back(Args&&... args) {
+    ops.emplace_back(std::make_unique<T>(std::forward<Args>(args)...));
+  }
+  void emplace_back(std::unique_ptr<Operation> op) {
+    ops.emplace_back(std::move(op));
+  }
+  void h(Qubit q) { emplace_back<StandardOperation>(q, H); }
+  void x(Qubit q) { emplace_back<StandardOperation>(q, X); }
+  void cx(Control c, Qubit t) { emplace_back<StandardOperation>(c, t, X); }
+  void swap(Qubit a, Qubit b) { emplace_back<StandardOperation>(a, b, SWAP); }
+  void barrier() {
+    Targets all;
+    for (Qubit q = 0; q < getNqubits(); ++q) {
+      all.push_back(q);
+    }
+    emplace_back<StandardOperation>(all, Barrier);
+  }
+  void measure(Qubit q, Bit c) {
+    ops.emplace_back(std::make_unique<NonUnitaryOperation>(
+        Targets{q}, std::vector<Bit>{c}));
+  }
+
+  void dumpOpenQASM(std::ostream& of, bool = true) const {
+    of << "OPENQASM 3.0;\ninclude \"stdgates.inc\";\n";
+    of << "qubit[" << getNqubits() << "] q;\n";
+    const QubitIndexToRegisterMap qm;
+    const BitIndexToRegisterMap cm;
+    for (const auto& op : ops) {
+      if (op->getType() == Measure) {
+        of << "// measure q[" << op->getTargets().at(0) << "]\n";
+        continue;
+      }
+      op->dumpOpenQASM(of, qm, cm, 0, true);
+    }
+  }
+  void dump(const std::string& filename, Format = Format::OpenQASM3) const {
+    std::ofstream of(filename);
+    if (of.good()) {
+      dumpOpenQASM(of);
+    }
+  }
+};
+} // namespace qc
