@@ -33,7 +33,9 @@ typedef enum {
   QMG_OOM = 5,
   /* the per-instance node pool is full (raise qmg_route_options.pool_nodes) */
   QMG_POOL_EXHAUSTED = 6,
-  QMG_NO_DEVICE = 7
+  QMG_NO_DEVICE = 7,
+  /* a caller-provided output buffer (swaps / placements) is too small */
+  QMG_BUFFER_TOO_SMALL = 8
 } qmg_status;
 
 /* include/sc/configuration/Heuristic.hpp:17-36 (same order) */
@@ -213,6 +215,26 @@ typedef struct {
   const uint32_t* gate1q_offsets; /* n_layers+1 */
   const qmg_gate1q* gates1q;
 } qmg_layers;
+
+/*
+ * Layered circuit: Mapper::createLayers (src/sc/Mapper.cpp:138-281) on a gate
+ * list over logical qubits (control[i] = -1 for a single-qubit gate), with
+ * the multiplicities of :237-280.  Host-only; the CSR view stays valid until
+ * the circuit is split or destroyed.
+ */
+typedef struct qmg_circuit qmg_circuit;
+int qmg_circuit_create(uint32_t nArchQubits, size_t nGates,
+                       const int32_t* control, const int32_t* target,
+                       int32_t layering /* qmg_layering */, qmg_circuit** out);
+int qmg_circuit_layers(const qmg_circuit* circ, qmg_layers* out);
+/* gate indices of every layer: offsets n_layers+1, indices nGates */
+int qmg_circuit_layer_gates(const qmg_circuit* circ, uint32_t* offsets,
+                            uint32_t* gateIndices);
+/* Mapper::isLayerSplittable (src/sc/Mapper.cpp:283-300) */
+int qmg_circuit_layer_splittable(const qmg_circuit* circ, uint32_t layer);
+/* Mapper::splitLayer (src/sc/Mapper.cpp:302-435): layer -> layer, layer+1 */
+int qmg_circuit_split_layer(qmg_circuit* circ, uint32_t layer);
+void qmg_circuit_destroy(qmg_circuit* circ);
 
 /* one search unit: a circuit, a start layout and a pass schedule */
 typedef struct {

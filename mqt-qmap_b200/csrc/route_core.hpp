@@ -1,0 +1,1583 @@
+// route_core.hpp - the A* SWAP search of one routing instance, written once
+// against a small "lane group" abstraction.
+//
+// Compiled by nvcc with a 32-lane warp group (route.cu: the shipped sm_100a
+// kernel, one warp per resident search) and by g++ with a 1-lane group
+// (tests/emu: a host build of the SAME source used only to debug the search
+// logic under ASan/UBSan where no GPU exists; it is not part of the product
+// library and nothing in the product path can reach it).
+//
+// Reference semantics reproduced (paths relative to the reference tree):
+//   aStarMap                src/sc/heuristic/HeuristicMapper.cpp:521-696
+//   expandNode              :698-727   expandNodeAddOneSwap :729-748
+//   applySWAP               :861-973   updateSharedSwaps    :975-1053
+//   recalculateFixedCost*   :750-859   heuristics           :1055-1354
+//   lookahead               :1356-1513 mapUnmappedGates     :211-307
+//   node order / identity   include/sc/heuristic/HeuristicMapper.hpp:438-483
+//   open list               include/sc/heuristic/UniquePriorityQueue.hpp:59-93
+#pragma once
+#include <stdint.h>
+#include <float.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define QMG_HD __host__ __device__ __forceinline__
+#define QMG_D __device__ __forceinline__
+#else
+#define QMG_HD inline
+#define QMG_D inline
+#endif
+
+namespace qmg {
+
+constexpr double kCostUniSwap = 34.0;  // Architecture.hpp:37 COST_UNIDIRECTIONAL_SWAP
+constexpr double kCostBiSwap = 30.0;   // Architecture.hpp:39 COST_BIDIRECTIONAL_SWAP
+constexpr uint32_t kCostReverse = 4U;  // Architecture.hpp:40 COST_DIRECTION_REVERSE
+constexpr double kTol = 1e-6;          // HeuristicMapper.hpp:463,473
+constexpr uint32_t kNone = 0xFFFFFFFFU;
+constexpr int kChunk = 32;    // children scored per pass
+constexpr int kLookBlock = 16; // lookahead layers scored per pass
+
+enum Status : int32_t {
+  ST_OK = 0,
+  ST_NO_VIABLE = 1,
+  ST_SPLIT = 2,
+  ST_BAD_ARG = 3,
+  ST_POOL = 6,
+  ST_BUFFER = 8,
+};
+
+struct Gate2 {
+  uint16_t q1, q2, fwd, rev;
+};
+struct Gate1 {
+  uint16_t q, mult;
+};
+
+// device-resident Architecture (include/sc/Architecture.hpp:42)
+struct ArchView {
+  int32_t n, nE;
+  int32_t bidirectional, unidirectional, fidelity, nFid;
+  const uint16_t* edges;   // 2*nE, ascending (first, second)
+  const uint32_t* incOff;  // n+1
+  const uint32_t* inc;     // ids of the directed edges touching p, ascending
+  const uint8_t* adj;      // n*n; bit0: (r,c) in coupling map, bit1: (c,r)
+  const double* dist;      // getDistanceTable(false)
+  const double* distRev;   // getDistanceTable(true)
+  const double* c1;        // singleQubitFidelityCosts
+  const double* c2;        // twoQubitFidelityCosts
+  const double* cswap;     // swapFidelityCosts
+  const double* fid;       // fidelityDistanceTables, nFid*n*n
+};
+
+struct CfgView {
+  int32_t heuristic, lookahead;
+  uint32_t nrLookaheads;
+  int32_t earlyTermination;
+  double firstFactor, factor;
+  uint64_t earlyLimit;
+  uint64_t splitLimit;
+  int32_t autoSplit;
+  int32_t tight, fidelityAware;
+};
+
+// layers of one circuit (Mapper::createLayers, src/sc/Mapper.cpp:138-281)
+struct CircView {
+  uint32_t nLayers, nLogical;
+  const uint32_t* g2Off;
+  const Gate2* g2;
+  const uint32_t* g1Off;
+  const Gate1* g1;
+  const uint32_t* consOff;  // getConsideredQubits(layer), ascending
+  const uint16_t* cons;
+  const uint32_t* next2q;   // Mapper::getNextLayer
+  const uint8_t* splittable;  // Mapper::isLayerSplittable
+};
+
+struct LayerOut {  // == qmg_layer_result
+  double cost_fixed, cost_fixed_reversals, cost_heur, lookahead_penalty;
+  uint64_t expanded, generated, expAfterFirst, expAfterOpt, solNodes,
+      solAfterOpt, layoutHash;
+  uint32_t depth, resultId, swapOff, nSwaps, placeOff, nPlace;
+  int32_t early, status;
+};
+
+struct InstView {
+  CircView circ;
+  const int16_t* initLoc;  // n or null
+  uint32_t passes;         // bidirectional pseudo-routing passes
+  uint32_t firstLayer, nRoute;
+  // outputs
+  LayerOut* layers;
+  uint16_t* swaps;
+  uint32_t swapCap;
+  uint16_t* places;
+  uint32_t placeCap;
+  int16_t* finalQ;
+  int16_t* finalL;
+  int16_t* startL;
+  int16_t* layerQ;
+  // [0]=nSwapsTotal [1]=nPlaceTotal [2]=nLayersDone [3]=status
+  uint32_t* summary;
+  uint64_t* counters;  // [0]=expanded [1]=generated (all passes)
+};
+
+struct NodeHdr {  // 72 bytes, followed by qubits[n], locations[n]
+  double fixed, rev, heur, look;
+  uint64_t hash;
+  uint32_t parent, shared;
+  uint32_t depth;
+  uint16_t swA, swB;
+  uint16_t nValid, flags;  // flags bit0 valid, bit1 open
+  uint32_t openPos;
+  uint32_t id, pad;
+};
+static_assert(sizeof(NodeHdr) == 72, "NodeHdr layout");
+
+struct OpenEntry {
+  double f, h2;
+  uint32_t idx;
+  uint16_t nValid;
+  uint16_t valid;
+};
+
+struct Child {
+  double fixed, rev, heur, look;
+  uint64_t hash;
+  uint32_t shared;
+  uint16_t a, b;
+  uint16_t nValid, valid;
+  uint32_t pad;
+};
+
+// per resident search, in global memory
+struct SearchMem {
+  uint8_t* pool;
+  OpenEntry* open;
+  uint64_t* table;
+  int16_t* curQ;
+  int16_t* curL;
+  uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
+  uint32_t poolCap, recBytes, tableMask, stamp;
+  uint32_t maxG;
+};
+
+// per resident search, in shared memory (device) / plain arrays (host)
+struct Scratch {
+  int16_t* Q;
+  int16_t* L;
+  uint32_t* consMask;
+  Child* ch;
+  double* lookPen;       // (kChunk / 2) * kLookBlock
+  uint32_t* lookLayers;  // kLookBlock + 2
+};
+
+QMG_HD uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ULL;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+  return x ^ (x >> 31);
+}
+// layout hash: sum over physical qubits of mix(p, qubits[p]); updated
+// incrementally per SWAP.  Also reported as qmg_layer_result.layout_hash.
+QMG_HD uint64_t cellHash(int p, int q) {
+  return mix64((static_cast<uint64_t>(static_cast<uint32_t>(p)) << 16) |
+               static_cast<uint16_t>(q));
+}
+
+// ---------------------------------------------------------------------------
+// lane groups
+// ---------------------------------------------------------------------------
+#if defined(__CUDA_ARCH__)
+struct Group {
+  static constexpr int W = 32;
+  int lane;
+  QMG_D Group() : lane(static_cast<int>(threadIdx.x) & 31) {}
+  QMG_D void sync() const { __syncwarp(); }
+  QMG_D uint32_t ballot(bool p) const { return __ballot_sync(0xffffffffU, p); }
+  QMG_D bool any(bool p) const { return __any_sync(0xffffffffU, p); }
+  template <class T> QMG_D T bcast(T v, int src) const {
+    return __shfl_sync(0xffffffffU, v, src);
+  }
+  template <class T> QMG_D T down(T v, int d) const {
+    return __shfl_down_sync(0xffffffffU, v, d);
+  }
+  template <class T> QMG_D T xorv(T v, int d) const {
+    return __shfl_xor_sync(0xffffffffU, v, d);
+  }
+};
+#else
+struct Group {
+  static constexpr int W = 1;
+  int lane = 0;
+  void sync() const {}
+  uint32_t ballot(bool p) const { return p ? 1U : 0U; }
+  bool any(bool p) const { return p; }
+  template <class T> T bcast(T v, int) const { return v; }
+  template <class T> T down(T v, int) const { return v; }
+  template <class T> T xorv(T v, int) const { return v; }
+};
+#endif
+
+template <class T> QMG_HD T ldg(const T* p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+QMG_HD Gate2 ldGate(const Gate2* p) {
+#if defined(__CUDA_ARCH__)
+  const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+  Gate2 g;
+  g.q1 = static_cast<uint16_t>(v.x & 0xffffU);
+  g.q2 = static_cast<uint16_t>(v.x >> 16);
+  g.fwd = static_cast<uint16_t>(v.y & 0xffffU);
+  g.rev = static_cast<uint16_t>(v.y >> 16);
+  return g;
+#else
+  return *p;
+#endif
+}
+
+QMG_HD double gmin(const Group& g, double v) {
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    const double o = g.xorv(v, d);
+    v = o < v ? o : v;
+  }
+  return v;
+}
+QMG_HD double gmax(const Group& g, double v) {
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    const double o = g.xorv(v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+QMG_HD uint64_t gsum64(const Group& g, uint64_t v) {
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    v += g.xorv(v, d);
+  }
+  return v;
+}
+// (value, index) argmin; ties -> smallest index ("first strict minimum")
+QMG_HD void gargmin(const Group& g, double& v, uint32_t& i) {
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    const double ov = g.xorv(v, d);
+    const uint32_t oi = g.xorv(i, d);
+    if (ov < v || (ov == v && oi < i)) {
+      v = ov;
+      i = oi;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// the search of one instance
+// ---------------------------------------------------------------------------
+struct Search {
+  const ArchView& A;
+  const CfgView& C;
+  const InstView& I;
+  SearchMem& M;
+  Scratch& S;
+  Group g;
+  int n;
+
+  // state of the running aStarMap call
+  uint32_t layer = 0;
+  uint32_t nPool = 0, nOpen = 0, nextId = 0;
+  uint32_t G = 0;  // 2q gates in the layer
+  const Gate2* gates = nullptr;
+  const Gate1* gates1 = nullptr;
+  uint32_t G1 = 0;
+  const uint16_t* cons = nullptr;
+  uint32_t nCons = 0;
+  uint32_t fidK = 0;  // table index |considered|-1 (kNone => cost 0)
+  uint32_t nLook = 0;
+
+  QMG_HD Search(const ArchView& a, const CfgView& c, const InstView& i,
+                SearchMem& m, Scratch& s)
+      : A(a), C(c), I(i), M(m), S(s), n(a.n) {}
+
+  // ---- table accessors (include/sc/Architecture.hpp:244-256,301-316,427-433)
+  QMG_HD bool adjU(int a, int b) const { return ldg(A.adj + a * n + b) != 0; }
+  QMG_HD bool adjD(int a, int b) const {
+    return (ldg(A.adj + a * n + b) & 1U) != 0;
+  }
+  QMG_HD double dRev(int a, int b) const { return ldg(A.distRev + a * n + b); }
+  QMG_HD double dPlain(int a, int b) const { return ldg(A.dist + a * n + b); }
+  QMG_HD double fidDist(int a, int b, uint32_t k) const {
+    if (k >= static_cast<uint32_t>(A.nFid)) {
+      return 0.;
+    }
+    return ldg(A.fid + (static_cast<size_t>(k) * n + a) * n + b);
+  }
+  QMG_HD double swapCostGC(int a, int b) const {
+    // applySWAP :957-964 / recalculateFixedCostNonFidelity :807-815
+    if (A.bidirectional) {
+      return kCostBiSwap;
+    }
+    if (A.unidirectional || ldg(A.adj + a * n + b) != 3U) {
+      return kCostUniSwap;
+    }
+    return kCostBiSwap;
+  }
+
+  QMG_HD NodeHdr* hdr(uint32_t idx) const {
+    return reinterpret_cast<NodeHdr*>(M.pool +
+                                      static_cast<size_t>(idx) * M.recBytes);
+  }
+  QMG_HD int16_t* nodeQ(uint32_t idx) const {
+    return reinterpret_cast<int16_t*>(
+        M.pool + static_cast<size_t>(idx) * M.recBytes + sizeof(NodeHdr));
+  }
+  QMG_HD int16_t* nodeL(uint32_t idx) const { return nodeQ(idx) + n; }
+  QMG_HD bool considered(int q) const {
+    return (S.consMask[q >> 5] >> (q & 31)) & 1U;
+  }
+
+  // ------------------------------------------------------------------------
+  // scoring of one node: the parent layout (S.Q / S.L) with the SWAP on the
+  // physical edge (a, b) applied; a == b scores the layout itself (root).
+  // Executed by ONE lane (gate-count heuristics).
+  // ------------------------------------------------------------------------
+  struct ParentCosts {
+    double fixed;
+    uint32_t shared;
+  };
+
+  QMG_HD int locAfter(int q, int q1, int q2, int a, int b) const {
+    if (q == q1) {
+      return b;
+    }
+    if (q == q2) {
+      return a;
+    }
+    return S.L[q];
+  }
+
+  // updateSharedSwaps :975-1053 (state before the swap)
+  QMG_HD uint32_t sharedSwapDelta(int a, int b, int q1, int q2) const {
+    if (q1 < 0 || q2 < 0 || !considered(q1) || !considered(q2)) {
+      return 0;
+    }
+    int p1 = q1;
+    int p2 = q2;
+    for (uint32_t i = 0; i < G; ++i) {
+      const Gate2 e = ldGate(gates + i);
+      if (e.q1 == q1) {
+        p1 = e.q2;
+      } else if (e.q2 == q1) {
+        p1 = e.q1;
+      }
+      if (e.q1 == q2) {
+        p2 = e.q2;
+      } else if (e.q2 == q2) {
+        p2 = e.q1;
+      }
+    }
+    if (p1 != q1 && p2 != q2 && p1 != q2) {
+      const int physQ3 = S.L[p1];
+      const int physQ4 = S.L[p2];
+      double e1b, e1n, e2b, e2n;
+      if (C.fidelityAware) {
+        e1b = fmin(fidDist(a, physQ3, 0), fidDist(physQ3, a, 0));
+        e1n = fmin(fidDist(b, physQ3, 0), fidDist(physQ3, b, 0));
+        e2b = fmin(fidDist(b, physQ4, 0), fidDist(physQ4, b, 0));
+        e2n = fmin(fidDist(a, physQ4, 0), fidDist(physQ4, a, 0));
+      } else {
+        e1b = fmin(dPlain(a, physQ3), dPlain(physQ3, a));
+        e1n = fmin(dPlain(b, physQ3), dPlain(physQ3, b));
+        e2b = fmin(dPlain(b, physQ4), dPlain(physQ4, b));
+        e2n = fmin(dPlain(a, physQ4), dPlain(physQ4, a));
+      }
+      if (e1n < e1b && e2n < e2b) {
+        return 1;
+      }
+    }
+    return 0;
+  }
+
+  // heuristicGateCountSumDistanceMinusSharedSwaps :1166-1253 given the
+  // per-gate swap counts in nsw[0..cnt) (unsorted)
+  QMG_HD double sharedSwapReduction(uint16_t* nsw, uint32_t cnt,
+                                    uint32_t shared) const {
+    // std::sort(..., greater): insertion sort on small per-lane arrays
+    for (uint32_t i = 1; i < cnt; ++i) {
+      const uint16_t v = nsw[i];
+      uint32_t j = i;
+      while (j > 0 && nsw[j - 1] < v) {
+        nsw[j] = nsw[j - 1];
+        --j;
+      }
+      nsw[j] = v;
+    }
+    uint64_t maxShared = 0;
+    for (uint32_t i = 0; i + 1 < cnt; ++i) {
+      uint32_t edgeShared = 0;
+      for (uint32_t j = i + 1; j < cnt && edgeShared < nsw[i]; ++j) {
+        if (nsw[j] > 0) {
+          ++edgeShared;
+          --nsw[j];
+        }
+      }
+      maxShared += edgeShared;
+    }
+    if (shared < maxShared) {
+      maxShared -= shared;
+    } else {
+      maxShared = 0;
+    }
+    return static_cast<double>(
+        maxShared * (A.bidirectional ? static_cast<uint64_t>(30)
+                                     : static_cast<uint64_t>(34)));
+  }
+
+  QMG_HD void scoreGateCount(int a, int b, const ParentCosts& pc, Child& out,
+                             uint16_t* nsw) const {
+    const bool root = (a == b);
+    const int q1 = root ? -2 : S.Q[a];
+    const int q2 = root ? -2 : S.Q[b];
+    out.a = static_cast<uint16_t>(a);
+    out.b = static_cast<uint16_t>(b);
+    const int h = C.heuristic;
+    // Node::sharedSwaps is only read by heuristics 2 and 3 (:1237-1241)
+    out.shared = pc.shared;
+    if (!root && (h == 2 || h == 3)) {
+      out.shared += sharedSwapDelta(a, b, q1, q2);
+    }
+    out.fixed = root ? 0. : pc.fixed + swapCostGC(a, b);
+
+    const bool wantMax = (h == 0 || h == 3);
+    const bool wantSum = (h == 1);
+    const bool wantShared = (h == 2 || h == 3);
+    uint32_t nValid = 0;
+    uint32_t revFixed = 0;  // recalculateFixedCostReversals :771-796
+    double hMax = 0.;
+    double hSum = 0.;
+    double hShared = 0.;
+    double costReversals = 0.;
+    uint32_t cnt = 0;
+    for (uint32_t i = 0; i < G; ++i) {
+      const Gate2 e = ldGate(gates + i);
+      const int p1 = locAfter(e.q1, q1, q2, a, b);
+      const int p2 = locAfter(e.q2, q1, q2, a, b);
+      const uint32_t ad = ldg(A.adj + p1 * n + p2);
+      const bool valid = ad != 0;
+      nValid += valid ? 1U : 0U;
+      if (!A.bidirectional) {
+        if (valid) {
+          uint32_t r = 0;
+          if ((ad & 1U) == 0) {
+            r = e.fwd * kCostReverse;
+          } else if ((ad & 2U) == 0) {
+            r = e.rev * kCostReverse;
+          }
+          revFixed += r;
+          if (wantMax) {
+            hMax = fmax(hMax, static_cast<double>(r));
+          }
+          if (wantSum) {
+            hSum += r;
+          }
+        }
+      }
+      if (wantShared && A.unidirectional) {
+        costReversals += (e.fwd < e.rev ? e.fwd : e.rev) * kCostReverse;
+      }
+      if (!valid) {
+        if (wantMax) {
+          if (e.fwd > 0) {
+            hMax = fmax(hMax, dRev(p1, p2));
+          }
+          if (e.rev > 0) {
+            hMax = fmax(hMax, dRev(p2, p1));
+          }
+        }
+        if (wantSum) {
+          double sc;
+          if (e.fwd == 0) {
+            sc = dRev(p2, p1);
+          } else if (e.rev == 0) {
+            sc = dRev(p1, p2);
+          } else {
+            sc = fmax(dRev(p1, p2), dRev(p2, p1));
+          }
+          hSum += sc;
+        }
+        if (wantShared) {
+          double sc;
+          if (e.fwd == 0) {
+            sc = dPlain(p2, p1);
+          } else if (e.rev == 0) {
+            sc = dPlain(p1, p2);
+          } else {
+            sc = fmin(dPlain(p1, p2), dPlain(p2, p1));
+          }
+          hShared += sc;
+          nsw[cnt++] = static_cast<uint16_t>(static_cast<uint64_t>(
+              sc / (A.unidirectional ? kCostUniSwap : kCostBiSwap)));
+        }
+      }
+    }
+    // (on a bidirectional architecture the reference also feeds validly
+    // mapped gates through the distance branch, :1108-1116; adjacent qubits
+    // have edge-skip distance 0, so skipping them here is equivalent)
+    const bool validMapping = (nValid == G);
+    out.nValid = static_cast<uint16_t>(nValid);
+    out.valid = validMapping ? 1 : 0;
+    out.rev = 0.;
+    if (!A.bidirectional && validMapping) {
+      out.rev = static_cast<double>(revFixed);
+    }
+    double heur = 0.;
+    if (!validMapping) {
+      double hs = 0.;
+      if (wantShared) {
+        const double red = sharedSwapReduction(nsw, cnt, out.shared);
+        hs = fmax(0., hShared - red) + costReversals;
+      }
+      if (h == 0) {
+        heur = hMax;
+      } else if (h == 1) {
+        heur = hSum;
+      } else if (h == 2) {
+        heur = hs;
+      } else {
+        heur = fmax(hMax, hs);
+      }
+    }
+    out.heur = heur;
+  }
+
+  // lookaheadGateCountMaxDistance / SumDistance :1387-1513 for one later
+  // layer and one child layout.  Executed by ONE lane.
+  QMG_HD double lookaheadPenalty(uint32_t ll, int a, int b, int q1,
+                                 int q2) const {
+    const uint32_t lo = ldg(I.circ.g2Off + ll);
+    const uint32_t hi = ldg(I.circ.g2Off + ll + 1);
+    const bool isMax = (C.lookahead == 1);
+    double penalty = 0.;
+    for (uint32_t i = lo; i < hi; ++i) {
+      const Gate2 e = ldGate(I.circ.g2 + i);
+      const int loc1 = locAfter(e.q1, q1, q2, a, b);
+      const int loc2 = locAfter(e.q2, q1, q2, a, b);
+      double cost;
+      if (loc1 < 0 && loc2 < 0) {
+        continue;
+      }
+      if (loc1 < 0 || loc2 < 0) {
+        // the placed partner; the other one may go to any free qubit
+        const bool firstFree = loc1 < 0;
+        const int loc = firstFree ? loc2 : loc1;
+        double mn = DBL_MAX;
+        for (int j = 0; j < n; ++j) {
+          const int qj = (j == a) ? q2 : ((j == b) ? q1 : S.Q[j]);
+          if (qj != -1) {
+            continue;
+          }
+          // :1405-1412 (loc1 free) and :1421-1428 (loc2 free)
+          if (e.fwd > 0) {
+            mn = fmin(mn, firstFree ? dRev(j, loc) : dRev(loc, j));
+          }
+          if (e.rev > 0) {
+            mn = fmin(mn, firstFree ? dRev(loc, j) : dRev(j, loc));
+          }
+        }
+        cost = mn;
+      } else {
+        cost = DBL_MAX;
+        if (e.fwd > 0) {
+          cost = fmin(cost, dRev(loc1, loc2));
+        }
+        if (e.rev > 0) {
+          cost = fmin(cost, dRev(loc2, loc1));
+        }
+      }
+      if (isMax) {
+        penalty = fmax(penalty, cost);
+      } else {
+        penalty += cost;
+      }
+    }
+    return penalty;
+  }
+
+  // updateLookaheadPenalty :1356-1385 for the cnt children in S.ch (or the
+  // root when rootOnly).  Items (child, lookahead layer) are spread over the
+  // lanes; the factor-weighted sum is then accumulated per child in layer
+  // order with the reference's operation order.
+  QMG_HD void scoreLookahead(int cnt, bool rootOnly) {
+    if (C.lookahead == 0) {
+      for (int c = g.lane; c < cnt; c += Group::W) {
+        S.ch[c].look = 0.;
+      }
+      g.sync();
+      return;
+    }
+    constexpr int kHalf = kChunk / 2;
+    for (int c0 = 0; c0 < cnt; c0 += kHalf) {
+      const int nc = (cnt - c0) < kHalf ? (cnt - c0) : kHalf;
+      uint32_t nextLayer = ldg(I.circ.next2q + layer);
+      double factor = C.firstFactor;
+      for (int c = g.lane; c < nc; c += Group::W) {
+        S.ch[c0 + c].look = 0.;
+      }
+      uint32_t done = 0;
+      while (done < C.nrLookaheads && nextLayer != kNone) {
+        // collect the next block of lookahead layers
+        uint32_t nb = 0;
+        if (g.lane == 0) {
+          uint32_t nl = nextLayer;
+          while (nb < static_cast<uint32_t>(kLookBlock) &&
+                 done + nb < C.nrLookaheads && nl != kNone) {
+            S.lookLayers[nb++] = nl;
+            nl = ldg(I.circ.next2q + nl);
+          }
+          S.lookLayers[kLookBlock] = nl;
+          S.lookLayers[kLookBlock + 1] = nb;
+        }
+        g.sync();
+        nb = S.lookLayers[kLookBlock + 1];
+        nextLayer = S.lookLayers[kLookBlock];
+        const int items = nc * static_cast<int>(nb);
+        for (int it = g.lane; it < items; it += Group::W) {
+          const int c = it / static_cast<int>(nb);
+          const int s = it - c * static_cast<int>(nb);
+          const Child& ch = S.ch[c0 + c];
+          int a = -1, b = -1, q1 = -2, q2 = -2;
+          if (!rootOnly) {
+            a = ch.a;
+            b = ch.b;
+            q1 = S.Q[a];
+            q2 = S.Q[b];
+          }
+          S.lookPen[c * kLookBlock + s] =
+              lookaheadPenalty(S.lookLayers[s], a, b, q1, q2);
+        }
+        g.sync();
+        for (int c = g.lane; c < nc; c += Group::W) {
+          double acc = S.ch[c0 + c].look;
+          double f = factor;
+          for (uint32_t s = 0; s < nb; ++s) {
+            acc += f * S.lookPen[c * kLookBlock + s];
+            f *= C.factor;
+          }
+          S.ch[c0 + c].look = acc;
+        }
+        for (uint32_t s = 0; s < nb; ++s) {
+          factor *= C.factor;
+        }
+        done += nb;
+        g.sync();
+      }
+    }
+    g.sync();
+  }
+
+  // ------------------------------------------------------------------------
+  // fidelity-aware scoring (recalculateFixedCostFidelity :821-859, the
+  // fidelity branches of applySWAP :893-952, heuristicFidelityBestLocation
+  // :1262-1354).  Executed by the WHOLE group for one child; the scans over
+  // physical qubits / coupling edges are spread over the lanes (min / max are
+  // exact, so the lane order does not matter), every ordered sum is done
+  // redundantly by all lanes in the reference's order.
+  // ------------------------------------------------------------------------
+  QMG_HD void scoreFidelity(int a, int b, const ParentCosts& pc, Child& out) {
+    const bool root = (a == b);
+    const int q1 = root ? -2 : S.Q[a];
+    const int q2 = root ? -2 : S.Q[b];
+    if (root) {
+      a = b = -1;
+    }
+    double fixed = root ? 0. : pc.fixed;
+    if (root) {
+      for (uint32_t i = 0; i < G1; ++i) {
+        const Gate1 e = ldg(gates1 + i);
+        fixed += e.mult * ldg(A.c1 + S.L[e.q]);
+      }
+    }
+    uint32_t nValid = 0;
+    for (uint32_t i = 0; i < G; ++i) {
+      const Gate2 e = ldGate(gates + i);
+      const int p3 = locAfter(e.q1, q1, q2, a, b);
+      const int p4 = locAfter(e.q2, q1, q2, a, b);
+      const bool valid = adjU(p3, p4);
+      nValid += valid ? 1U : 0U;
+      if (root) {
+        if (valid) {
+          fixed += (e.fwd * ldg(A.c2 + p3 * n + p4) +
+                    e.rev * ldg(A.c2 + p4 * n + p3));
+        }
+        continue;
+      }
+      const bool touched =
+          (e.q1 == q1 || e.q1 == q2 || e.q2 == q1 || e.q2 == q2);
+      if (!touched) {
+        continue;
+      }
+      const int o3 = S.L[e.q1];
+      const int o4 = S.L[e.q2];
+      const bool before = adjU(o3, o4);
+      if (valid && !before) {
+        fixed += e.fwd * ldg(A.c2 + p3 * n + p4) +
+                 e.rev * ldg(A.c2 + p4 * n + p3);
+      } else if (!valid && before) {
+        fixed -= e.fwd * ldg(A.c2 + o3 * n + o4) +
+                 e.rev * ldg(A.c2 + o4 * n + o3);
+      }
+    }
+    if (!root) {
+      // :934-952
+      int m1 = 0;
+      int m2 = 0;
+      for (uint32_t i = 0; i < G1; ++i) {
+        const Gate1 e = ldg(gates1 + i);
+        if (e.q == q1) {
+          m1 = e.mult;
+        }
+        if (e.q == q2) {
+          m2 = e.mult;
+        }
+      }
+      fixed += ((m2 - m1) * ldg(A.c1 + a) + (m1 - m2) * ldg(A.c1 + b));
+      fixed += ldg(A.cswap + a * n + b);
+    }
+
+    // heuristicFidelityBestLocation
+    double costHeur = 0.;
+    double savings = 0.;
+    for (uint32_t i = 0; i < G1; ++i) {
+      const Gate1 e = ldg(gates1 + i);
+      const int loc = locAfter(e.q, q1, q2, a, b);
+      const double curr = ldg(A.c1 + loc);
+      double best = 0.;
+      for (int p = g.lane; p < n; p += Group::W) {
+        const double cp = ldg(A.c1 + p);
+        if (cp >= curr) {
+          continue;
+        }
+        const double cur = e.mult * (curr - cp) - fidDist(loc, p, fidK);
+        best = fmax(best, cur);
+      }
+      best = gmax(g, best);
+      savings += best;
+    }
+    for (uint32_t i = 0; i < G; ++i) {
+      const Gate2 e = ldGate(gates + i);
+      const int l1 = locAfter(e.q1, q1, q2, a, b);
+      const int l2 = locAfter(e.q2, q1, q2, a, b);
+      double sc = DBL_MAX;
+      for (int k = g.lane; k < A.nE; k += Group::W) {
+        const int q3 = ldg(A.edges + 2 * k);
+        const int q4 = ldg(A.edges + 2 * k + 1);
+        const double c34 = ldg(A.c2 + q3 * n + q4);
+        const double c43 = ldg(A.c2 + q4 * n + q3);
+        const double v1 = e.fwd * c34 + e.rev * c43 + fidDist(l1, q3, fidK) +
+                          fidDist(l2, q4, fidK);
+        sc = fmin(sc, v1);
+        const double v2 = e.fwd * c43 + e.rev * c34 + fidDist(l2, q3, fidK) +
+                          fidDist(l1, q4, fidK);
+        sc = fmin(sc, v2);
+      }
+      sc = gmin(g, sc);
+      if (adjU(l1, l2)) {
+        const double currEdge = (e.fwd * ldg(A.c2 + l1 * n + l2) +
+                                 e.rev * ldg(A.c2 + l2 * n + l1));
+        savings += (currEdge - sc);
+      } else {
+        costHeur += sc;
+      }
+    }
+    out.a = static_cast<uint16_t>(a < 0 ? 0 : a);
+    out.b = static_cast<uint16_t>(b < 0 ? 0 : b);
+    out.fixed = fixed;
+    out.rev = 0.;
+    out.heur = costHeur - savings;
+    out.shared = 0;
+    out.nValid = static_cast<uint16_t>(nValid);
+    out.valid = (nValid == G) ? 1 : 0;
+  }
+
+  // ------------------------------------------------------------------------
+  // open list: UniquePriorityQueue semantics on (open[], table[], pool)
+  // ------------------------------------------------------------------------
+  // node order, HeuristicMapper.hpp:452-483, first four keys.
+  // returns -1 if x has priority, +1 if y has priority, 0 if tied
+  QMG_HD static int cmp4(const OpenEntry& x, const OpenEntry& y) {
+    if (fabs(x.f - y.f) > kTol) {
+      return x.f > y.f ? 1 : -1;
+    }
+    if (x.valid != y.valid) {
+      return y.valid ? 1 : -1;
+    }
+    if (fabs(x.h2 - y.h2) > kTol) {
+      return x.h2 > y.h2 ? 1 : -1;
+    }
+    if (x.nValid != y.nValid) {
+      return x.nValid < y.nValid ? 1 : -1;
+    }
+    return 0;
+  }
+  // full order incl. the lexicographic tie-break (:438-450, :482): among
+  // tied nodes the lexicographically LARGEST qubits[] is on top
+  QMG_HD bool hasPriority(const OpenEntry& x, const OpenEntry& y) const {
+    const int c = cmp4(x, y);
+    if (c != 0) {
+      return c < 0;
+    }
+    if (x.idx == y.idx) {
+      return false;
+    }
+    const int16_t* qx = nodeQ(x.idx);
+    const int16_t* qy = nodeQ(y.idx);
+    for (int i = 0; i < n; ++i) {
+      const int16_t vx = qx[i];
+      const int16_t vy = qy[i];
+      if (vx != vy) {
+        return vx > vy;
+      }
+    }
+    return false;
+  }
+
+  // position of the top of the open list (group-uniform result)
+  QMG_HD uint32_t topPos() const {
+    OpenEntry best;
+    uint32_t bestPos = kNone;
+    best.f = 0.;
+    best.h2 = 0.;
+    best.idx = kNone;
+    best.nValid = 0;
+    best.valid = 0;
+    for (uint32_t i = g.lane; i < nOpen; i += Group::W) {
+      const OpenEntry e = M.open[i];
+      if (bestPos == kNone || hasPriority(e, best)) {
+        best = e;
+        bestPos = i;
+      }
+    }
+    for (int d = Group::W / 2; d > 0; d >>= 1) {
+      OpenEntry o;
+      o.f = g.xorv(best.f, d);
+      o.h2 = g.xorv(best.h2, d);
+      o.idx = g.xorv(best.idx, d);
+      const uint32_t pk = g.xorv(
+          (static_cast<uint32_t>(best.nValid) << 16) | best.valid, d);
+      o.nValid = static_cast<uint16_t>(pk >> 16);
+      o.valid = static_cast<uint16_t>(pk & 0xffffU);
+      const uint32_t op = g.xorv(bestPos, d);
+      if (op != kNone && (bestPos == kNone || hasPriority(o, best))) {
+        best = o;
+        bestPos = op;
+      }
+    }
+    return bestPos;
+  }
+
+  QMG_HD void removeOpen(uint32_t pos) {
+    // group-uniform; lane 0 writes
+    const uint32_t last = nOpen - 1;
+    if (g.lane == 0) {
+      const uint32_t idx = M.open[pos].idx;
+      hdr(idx)->flags &= static_cast<uint16_t>(~2U);
+      if (pos != last) {
+        const OpenEntry e = M.open[last];
+        M.open[pos] = e;
+        hdr(e.idx)->openPos = pos;
+      }
+    }
+    nOpen = last;
+    g.sync();
+  }
+
+  // write a node record: parent layout (S.Q/S.L) with the child's swap
+  QMG_HD void writeNode(uint32_t idx, const Child& ch, uint32_t parentIdx,
+                        uint32_t depth, uint32_t id, uint32_t openPos,
+                        bool root) {
+    int16_t* q = nodeQ(idx);
+    int16_t* l = nodeL(idx);
+    const int a = ch.a;
+    const int b = ch.b;
+    const int q1 = root ? -2 : S.Q[a];
+    const int q2 = root ? -2 : S.Q[b];
+    for (int i = g.lane; i < n; i += Group::W) {
+      int16_t vq = S.Q[i];
+      int16_t vl = S.L[i];
+      if (!root) {
+        if (i == a) {
+          vq = static_cast<int16_t>(q2);
+        } else if (i == b) {
+          vq = static_cast<int16_t>(q1);
+        }
+        if (i == q1) {
+          vl = static_cast<int16_t>(b);
+        } else if (i == q2) {
+          vl = static_cast<int16_t>(a);
+        }
+      }
+      q[i] = vq;
+      l[i] = vl;
+    }
+    if (g.lane == 0) {
+      NodeHdr* h = hdr(idx);
+      h->fixed = ch.fixed;
+      h->rev = ch.rev;
+      h->heur = ch.heur;
+      h->look = ch.look;
+      h->hash = ch.hash;
+      h->parent = parentIdx;
+      h->shared = ch.shared;
+      h->depth = depth;
+      h->swA = ch.a;
+      h->swB = ch.b;
+      h->nValid = ch.nValid;
+      h->flags = static_cast<uint16_t>((ch.valid ? 1U : 0U) | 2U);
+      h->openPos = openPos;
+      h->id = id;
+      h->pad = 0;
+    }
+  }
+
+  QMG_HD static OpenEntry entryOf(const Child& ch, uint32_t idx) {
+    OpenEntry e;
+    e.f = ch.fixed + ch.rev + ch.heur + ch.look;  // Node::getTotalCost
+    e.h2 = ch.heur + ch.look;
+    e.idx = idx;
+    e.nValid = ch.nValid;
+    e.valid = ch.valid;
+    return e;
+  }
+
+  // does the stored node idx have the layout "parent with ch's swap"?
+  QMG_HD bool sameLayout(uint32_t idx, const Child& ch, bool root) const {
+    const int16_t* q = nodeQ(idx);
+    const int a = ch.a;
+    const int b = ch.b;
+    bool diff = false;
+    for (int i0 = 0; i0 < n; i0 += Group::W) {
+      const int i = i0 + g.lane;
+      if (i < n) {
+        int16_t v = S.Q[i];
+        if (!root) {
+          if (i == a) {
+            v = S.Q[b];
+          } else if (i == b) {
+            v = S.Q[a];
+          }
+        }
+        diff = diff || (q[i] != v);
+      }
+      if (g.any(diff)) {
+        return false;
+      }
+    }
+    return true;
+  }
+
+  // UniquePriorityQueue::push :59-82.  Group-uniform.  Returns false when the
+  // node pool is exhausted.
+  QMG_HD bool push(const Child& ch, uint32_t parentIdx, uint32_t depth,
+                   bool root) {
+    const uint32_t id = nextId++;
+    const uint64_t h = ch.hash;
+    uint32_t slot = static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
+    uint32_t found = kNone;
+    for (;;) {
+      const uint64_t e = M.table[slot];
+      if (static_cast<uint32_t>(e >> 32) != M.stamp) {
+        break;  // free slot
+      }
+      const uint32_t idx = static_cast<uint32_t>(e);
+      if (hdr(idx)->hash == h && sameLayout(idx, ch, root)) {
+        found = idx;
+        break;
+      }
+      slot = (slot + 1) & M.tableMask;
+    }
+    if (found != kNone && (hdr(found)->flags & 2U) != 0) {
+      // layout is in the open list: keep the better one (:63-79)
+      const uint32_t pos = hdr(found)->openPos;
+      const OpenEntry ex = M.open[pos];
+      const OpenEntry ne = entryOf(ch, found);
+      if (cmp4(ne, ex) < 0) {
+        // existing > new: replace in place (the old node was never expanded,
+        // so nothing refers to its record)
+        g.sync();
+        writeNode(found, ch, parentIdx, depth, id, pos, root);
+        if (g.lane == 0) {
+          M.open[pos] = ne;
+        }
+        g.sync();
+      }
+      return true;
+    }
+    if (nPool >= M.poolCap) {
+      return false;
+    }
+    const uint32_t idx = nPool++;
+    const uint32_t pos = nOpen++;
+    writeNode(idx, ch, parentIdx, depth, id, pos, root);
+    if (g.lane == 0) {
+      M.open[pos] = entryOf(ch, idx);
+      M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | idx;
+    }
+    g.sync();
+    return true;
+  }
+
+  // score the cnt children in S.ch (their a/b are set) and push them in order
+  QMG_HD bool flushChildren(int cnt, uint32_t parentIdx, const ParentCosts& pc,
+                            uint64_t parentHash, uint32_t depth) {
+    g.sync();
+    if (C.fidelityAware) {
+      for (int c = 0; c < cnt; ++c) {
+        Child out;
+        scoreFidelity(S.ch[c].a, S.ch[c].b, pc, out);
+        if (g.lane == 0) {
+          S.ch[c].fixed = out.fixed;
+          S.ch[c].rev = out.rev;
+          S.ch[c].heur = out.heur;
+          S.ch[c].shared = 0;
+          S.ch[c].nValid = out.nValid;
+          S.ch[c].valid = out.valid;
+        }
+      }
+    } else {
+      for (int c = g.lane; c < cnt; c += Group::W) {
+        Child out;
+        scoreGateCount(S.ch[c].a, S.ch[c].b, pc, out,
+                       M.nsw + static_cast<size_t>(g.lane) * M.maxG);
+        S.ch[c].fixed = out.fixed;
+        S.ch[c].rev = out.rev;
+        S.ch[c].heur = out.heur;
+        S.ch[c].shared = out.shared;
+        S.ch[c].nValid = out.nValid;
+        S.ch[c].valid = out.valid;
+      }
+    }
+    for (int c = g.lane; c < cnt; c += Group::W) {
+      const int a = S.ch[c].a;
+      const int b = S.ch[c].b;
+      const int q1 = S.Q[a];
+      const int q2 = S.Q[b];
+      S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
+                     cellHash(a, q2) + cellHash(b, q1);
+    }
+    g.sync();
+    scoreLookahead(cnt, false);
+    for (int c = 0; c < cnt; ++c) {
+      const Child ch = S.ch[c];
+      if (!push(ch, parentIdx, depth, false)) {
+        return false;
+      }
+    }
+    return true;
+  }
+
+  // expandNode :698-727.  The candidate order (considered qubit ascending,
+  // then coupling edge ascending) and the usedSwaps rule are reproduced by a
+  // closed form: a swap between two occupied physical qubits is generated
+  // only from the smallest considered qubit of the pair and only on the
+  // smaller of the (up to two) directed edges between them.
+  QMG_HD bool expand(uint32_t parentIdx) {
+    // stage the parent
+    const int16_t* pq = nodeQ(parentIdx);
+    const int16_t* pl = nodeL(parentIdx);
+    for (int i = g.lane; i < n; i += Group::W) {
+      S.Q[i] = pq[i];
+      S.L[i] = pl[i];
+    }
+    const NodeHdr* ph = hdr(parentIdx);
+    ParentCosts pc;
+    pc.fixed = ph->fixed;
+    pc.shared = ph->shared;
+    const uint64_t parentHash = ph->hash;
+    const uint32_t depth = ph->depth + 1;
+    g.sync();
+    int cnt = 0;
+    for (uint32_t ci = 0; ci < nCons; ++ci) {
+      const int q = ldg(cons + ci);
+      const int p = S.L[q];
+      if (p < 0) {
+        continue;
+      }
+      const uint32_t lo = ldg(A.incOff + p);
+      const uint32_t hi = ldg(A.incOff + p + 1);
+      for (uint32_t k0 = lo; k0 < hi; k0 += Group::W) {
+        const uint32_t k = k0 + g.lane;
+        bool keep = false;
+        int ea = 0;
+        int eb = 0;
+        if (k < hi) {
+          const uint32_t e = ldg(A.inc + k);
+          ea = ldg(A.edges + 2 * e);
+          eb = ldg(A.edges + 2 * e + 1);
+          const int qa = S.Q[ea];
+          const int qb = S.Q[eb];
+          if (qa == -1 || qb == -1) {
+            keep = true;
+          } else {
+            const int other = (qa == q) ? qb : qa;
+            const bool otherFirst = considered(other) && other < q;
+            const bool twinFirst =
+                (eb < ea) && ((ldg(A.adj + ea * n + eb) & 2U) != 0);
+            keep = !otherFirst && !twinFirst;
+          }
+        }
+        const uint32_t bal = g.ballot(keep);
+        const int add = __builtin_popcount(bal);
+        if (add == 0) {
+          continue;
+        }
+        if (cnt + add > kChunk) {
+          if (!flushChildren(cnt, parentIdx, pc, parentHash, depth)) {
+            return false;
+          }
+          cnt = 0;
+        }
+        if (keep) {
+          const int rank =
+              __builtin_popcount(bal & ((1U << g.lane) - 1U));
+          S.ch[cnt + rank].a = static_cast<uint16_t>(ea);
+          S.ch[cnt + rank].b = static_cast<uint16_t>(eb);
+        }
+        cnt += add;
+      }
+    }
+    if (cnt > 0) {
+      if (!flushChildren(cnt, parentIdx, pc, parentHash, depth)) {
+        return false;
+      }
+    }
+    return true;
+  }
+
+  // ------------------------------------------------------------------------
+  // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on M.curQ / M.curL
+  // ------------------------------------------------------------------------
+  uint32_t nPlace = 0;  // running count into I.places
+  bool record = false;
+
+  QMG_HD void place(int logical, int phys) {
+    if (g.lane == 0) {
+      M.curQ[phys] = static_cast<int16_t>(logical);
+      M.curL[logical] = static_cast<int16_t>(phys);
+      if (record && I.places != nullptr && nPlace < I.placeCap) {
+        I.places[2 * nPlace] = static_cast<uint16_t>(logical);
+        I.places[2 * nPlace + 1] = static_cast<uint16_t>(phys);
+      }
+    }
+    if (record) {
+      ++nPlace;
+    }
+    g.sync();
+  }
+
+  QMG_HD int firstFree() const {
+    for (int p0 = 0; p0 < n; p0 += Group::W) {
+      const int p = p0 + g.lane;
+      const uint32_t bal = g.ballot(p < n && M.curQ[p] == -1);
+      if (bal != 0) {
+        return p0 + __builtin_ctz(bal);
+      }
+    }
+    return -1;
+  }
+
+  QMG_HD bool mapToMinDistance(int source, int target) {
+    const int src = M.curL[source];
+    double best = DBL_MAX;
+    uint32_t pos = kNone;
+    for (int i = g.lane; i < n; i += Group::W) {
+      if (M.curQ[i] == -1) {
+        const double d = dRev(src, i);
+        if (d < best) {
+          best = d;
+          pos = static_cast<uint32_t>(i);
+        }
+      }
+    }
+    gargmin(g, best, pos);
+    if (pos == kNone) {
+      return false;
+    }
+    place(target, static_cast<int>(pos));
+    return true;
+  }
+
+  QMG_HD bool mapUnmappedGates() {
+    g.sync();
+    if (C.fidelityAware) {
+      for (uint32_t i = 0; i < G1; ++i) {
+        const Gate1 e = ldg(gates1 + i);
+        if (M.curL[e.q] == -1) {
+          const int p = firstFree();
+          if (p >= 0) {
+            place(e.q, p);
+          }
+        }
+      }
+    }
+    for (uint32_t i = 0; i < G; ++i) {
+      const Gate2 e = ldGate(gates + i);
+      const int l1 = M.curL[e.q1];
+      const int l2 = M.curL[e.q2];
+      if (l1 == -1 && l2 == -1) {
+        // first coupling edge (ascending) with both ends free
+        int ca = -1;
+        int cb = -1;
+        for (int k0 = 0; k0 < A.nE; k0 += Group::W) {
+          const int k = k0 + g.lane;
+          bool ok = false;
+          if (k < A.nE) {
+            ok = M.curQ[ldg(A.edges + 2 * k)] == -1 &&
+                 M.curQ[ldg(A.edges + 2 * k + 1)] == -1;
+          }
+          const uint32_t bal = g.ballot(ok);
+          if (bal != 0) {
+            const int kk = k0 + __builtin_ctz(bal);
+            ca = ldg(A.edges + 2 * kk);
+            cb = ldg(A.edges + 2 * kk + 1);
+            break;
+          }
+        }
+        if (ca < 0) {
+          // two free qubits with minimal distance, first strict minimum in
+          // (i, j) order
+          double best = 2147483647.0;
+          uint32_t code = kNone;
+          for (int i = g.lane; i < n; i += Group::W) {
+            if (M.curQ[i] != -1) {
+              continue;
+            }
+            for (int j = i + 1; j < n; ++j) {
+              if (M.curQ[j] != -1) {
+                continue;
+              }
+              const double d = dRev(i, j);
+              const uint32_t cd = static_cast<uint32_t>(i) * n + j;
+              if (d < best || (d == best && cd < code)) {
+                best = d;
+                code = cd;
+              }
+            }
+          }
+          gargmin(g, best, code);
+          if (code == kNone) {
+            return false;
+          }
+          ca = static_cast<int>(code / n);
+          cb = static_cast<int>(code % n);
+        }
+        place(e.q1, ca);
+        place(e.q2, cb);
+      } else if (l1 == -1) {
+        if (!mapToMinDistance(e.q2, e.q1)) {
+          return false;
+        }
+      } else if (l2 == -1) {
+        if (!mapToMinDistance(e.q1, e.q2)) {
+          return false;
+        }
+      }
+    }
+    return true;
+  }
+
+  // ------------------------------------------------------------------------
+  // aStarMap :521-696
+  // ------------------------------------------------------------------------
+  struct LayerStats {
+    uint64_t expanded = 0, expAfterFirst = 0, expAfterOpt = 0, solNodes = 0,
+             solAfterOpt = 0;
+    uint32_t result = kNone;
+    int32_t early = 0;
+  };
+
+  QMG_HD void setLayer(uint32_t l) {
+    layer = l;
+    const uint32_t lo = ldg(I.circ.g2Off + l);
+    G = ldg(I.circ.g2Off + l + 1) - lo;
+    gates = I.circ.g2 + lo;
+    const uint32_t lo1 = ldg(I.circ.g1Off + l);
+    G1 = ldg(I.circ.g1Off + l + 1) - lo1;
+    gates1 = I.circ.g1 + lo1;
+    const uint32_t loc = ldg(I.circ.consOff + l);
+    nCons = ldg(I.circ.consOff + l + 1) - loc;
+    cons = I.circ.cons + loc;
+    fidK = nCons == 0 ? kNone : nCons - 1;
+    g.sync();
+    for (int w = g.lane; w < (n + 31) / 32; w += Group::W) {
+      S.consMask[w] = 0;
+    }
+    g.sync();
+    if (g.lane == 0) {
+      for (uint32_t i = 0; i < nCons; ++i) {
+        const int q = ldg(cons + i);
+        S.consMask[q >> 5] |= 1U << (q & 31);
+      }
+    }
+    g.sync();
+  }
+
+  QMG_HD int astar(LayerStats& st) {
+    nPool = 0;
+    nOpen = 0;
+    nextId = 0;
+    ++M.stamp;
+    // root node from the mapper's current layout
+    for (int i = g.lane; i < n; i += Group::W) {
+      S.Q[i] = M.curQ[i];
+      S.L[i] = M.curL[i];
+    }
+    g.sync();
+    uint64_t hsh = 0;
+    for (int i = g.lane; i < n; i += Group::W) {
+      hsh += cellHash(i, S.Q[i]);
+    }
+    hsh = gsum64(g, hsh);
+    ParentCosts pc;
+    pc.fixed = 0.;
+    pc.shared = 0;
+    if (C.fidelityAware) {
+      Child out;
+      scoreFidelity(0, 0, pc, out);
+      if (g.lane == 0) {
+        S.ch[0] = out;
+      }
+    } else if (g.lane == 0) {
+      Child out;
+      scoreGateCount(0, 0, pc, out, M.nsw);
+      S.ch[0] = out;
+    }
+    g.sync();
+    if (g.lane == 0) {
+      S.ch[0].hash = hsh;
+      S.ch[0].a = 0;
+      S.ch[0].b = 0;
+    }
+    g.sync();
+    scoreLookahead(1, true);
+    {
+      const Child root = S.ch[0];
+      if (!push(root, kNone, 0, true)) {
+        return ST_POOL;
+      }
+    }
+    const bool splittable =
+        C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
+    bool found = false;
+    double bestFixedTotal = 0.;
+    for (;;) {
+      if (nOpen == 0) {
+        break;
+      }
+      const uint32_t pos = topPos();
+      const OpenEntry top = M.open[pos];
+      if (found && !(top.f < bestFixedTotal)) {
+        break;
+      }
+      if (splittable && st.expanded >= C.splitLimit) {
+        return ST_SPLIT;
+      }
+      const uint32_t cur = top.idx;
+      if (top.valid) {
+        ++st.solNodes;
+        const NodeHdr* h = hdr(cur);
+        const double fixedTotal = h->fixed + h->rev + h->look;
+        if (!found || fixedTotal < bestFixedTotal) {
+          st.result = cur;
+          bestFixedTotal = fixedTotal;
+          st.expAfterOpt = 0;
+          st.solAfterOpt = 0;
+        } else {
+          ++st.solAfterOpt;
+        }
+        found = true;
+        if (C.tight) {
+          break;
+        }
+      }
+      removeOpen(pos);
+      if (!expand(cur)) {
+        return ST_POOL;
+      }
+      ++st.expanded;
+      if (found) {
+        ++st.expAfterFirst;
+        ++st.expAfterOpt;
+        if (C.earlyTermination != 0) {
+          uint64_t v = 0;
+          switch (C.earlyTermination) {
+          case 1:
+            v = st.expanded;
+            break;
+          case 2:
+            v = st.expAfterFirst;
+            break;
+          case 3:
+            v = st.expAfterOpt;
+            break;
+          case 4:
+            v = st.solNodes;
+            break;
+          case 5:
+            v = st.solAfterOpt;
+            break;
+          default:
+            break;
+          }
+          if (v >= C.earlyLimit) {
+            st.early = 1;
+            break;
+          }
+        }
+      }
+    }
+    if (!found) {
+      return ST_NO_VIABLE;
+    }
+    return ST_OK;
+  }
+
+  // one aStarMap call incl. mapUnmappedGates; adopts the result layout
+  QMG_HD int routeLayer(uint32_t l, bool finalPass, uint32_t& swapTotal) {
+    setLayer(l);
+    const uint32_t placeBefore = nPlace;
+    record = finalPass;
+    if (!mapUnmappedGates()) {
+      return ST_BAD_ARG;
+    }
+    LayerStats st;
+    const int rc = astar(st);
+    if (g.lane == 0) {
+      I.counters[0] += st.expanded;
+      I.counters[1] += nextId;
+    }
+    if (rc != ST_OK) {
+      return rc;
+    }
+    const uint32_t res = st.result;
+    const NodeHdr* h = hdr(res);
+    const int16_t* rq = nodeQ(res);
+    const int16_t* rl = nodeL(res);
+    g.sync();
+    for (int i = g.lane; i < n; i += Group::W) {
+      M.curQ[i] = rq[i];
+      M.curL[i] = rl[i];
+      if (finalPass && I.layerQ != nullptr) {
+        I.layerQ[static_cast<size_t>(l) * n + i] = rq[i];
+      }
+    }
+    if (finalPass) {
+      const uint32_t d = h->depth;
+      if (g.lane == 0) {
+        LayerOut& o = I.layers[l];
+        o.cost_fixed = h->fixed;
+        o.cost_fixed_reversals = h->rev;
+        o.cost_heur = h->heur;
+        o.lookahead_penalty = h->look;
+        o.expanded = st.expanded;
+        o.generated = nextId;
+        o.expAfterFirst = st.expAfterFirst;
+        o.expAfterOpt = st.expAfterOpt;
+        o.solNodes = st.solNodes;
+        o.solAfterOpt = st.solAfterOpt;
+        o.layoutHash = h->hash;
+        o.depth = d;
+        o.resultId = h->id;
+        o.swapOff = swapTotal;
+        o.nSwaps = d;
+        o.placeOff = placeBefore;
+        o.nPlace = nPlace - placeBefore;
+        o.early = st.early;
+        o.status = ST_OK;
+        // swaps root -> result
+        if (I.swaps != nullptr && swapTotal + d <= I.swapCap) {
+          uint32_t cur = res;
+          for (uint32_t k = d; k > 0; --k) {
+            const NodeHdr* c = hdr(cur);
+            I.swaps[2 * (swapTotal + k - 1)] = c->swA;
+            I.swaps[2 * (swapTotal + k - 1) + 1] = c->swB;
+            cur = c->parent;
+          }
+        }
+      }
+      swapTotal += d;
+      if (I.swaps != nullptr && swapTotal > I.swapCap) {
+        return ST_BUFFER;
+      }
+    }
+    g.sync();
+    return ST_OK;
+  }
+
+  // HeuristicMapper::map :74-91 for one instance
+  QMG_HD void run() {
+    const uint32_t nL = I.circ.nLayers;
+    for (int i = g.lane; i < n; i += Group::W) {
+      M.curQ[i] = -1;
+      M.curL[i] = -1;
+    }
+    g.sync();
+    if (I.initLoc != nullptr) {
+      for (int i = g.lane; i < n; i += Group::W) {
+        const int16_t p = I.initLoc[i];
+        M.curL[i] = p;
+        if (p >= 0) {
+          M.curQ[p] = static_cast<int16_t>(i);
+        }
+      }
+    }
+    g.sync();
+    if (g.lane == 0) {
+      I.counters[0] = 0;
+      I.counters[1] = 0;
+    }
+    uint32_t swapTotal = 0;
+    int rc = ST_OK;
+    uint32_t doneLayers = 0;
+    for (uint32_t pass = 0; pass < I.passes && rc == ST_OK; ++pass) {
+      for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
+        rc = routeLayer(i, false, swapTotal);
+      }
+      for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
+        rc = routeLayer(nL - 1 - i, false, swapTotal);
+      }
+    }
+    if (rc == ST_OK) {
+      if (I.startL != nullptr) {
+        for (int i = g.lane; i < n; i += Group::W) {
+          I.startL[i] = M.curL[i];
+        }
+      }
+      const uint32_t first = I.firstLayer;
+      const uint32_t last =
+          (I.nRoute == 0 || first + I.nRoute > nL) ? nL : first + I.nRoute;
+      doneLayers = first;
+      for (uint32_t l = first; l < last; ++l) {
+        rc = routeLayer(l, true, swapTotal);
+        if (rc != ST_OK) {
+          break;
+        }
+        ++doneLayers;
+      }
+    }
+    g.sync();
+    for (int i = g.lane; i < n; i += Group::W) {
+      I.finalQ[i] = M.curQ[i];
+      I.finalL[i] = M.curL[i];
+    }
+    if (g.lane == 0) {
+      I.summary[0] = swapTotal;
+      I.summary[1] = nPlace;
+      I.summary[2] = doneLayers;
+      I.summary[3] = static_cast<uint32_t>(rc);
+    }
+    g.sync();
+  }
+};
+
+}  // namespace qmg

@@ -1,0 +1,162 @@
+// emu.cpp - HOST DEBUG BUILD of the routing kernel's source.
+//
+// TEST INFRASTRUCTURE ONLY.  Compiles mqt-qmap_b200/csrc/route_core.hpp (the
+// very code the sm_100a kernel runs, one warp per search) with a 1-lane group
+// so that the search logic can be exercised under ASan/UBSan and compared
+// with the reference in a container that has no GPU.  It is built into
+// tests/emu/libqmg_emu.so, is loaded only by tests/, is not linked into and
+// cannot be reached from the product library (libqmap_b200.so), and is never
+// timed.  Cost tables are INPUTS here (the table kernels exist only in CUDA).
+#define QMG_HOST_API_IMPL
+#include "../../mqt-qmap_b200/csrc/host_api.hpp"
+
+#include <memory>
+#include <vector>
+
+using namespace qmg;
+
+struct qemu_arch {
+  ArchTopology topo;
+  std::vector<double> dist, distRev, c1, c2, cswap, fid;
+  int nFid = 0;
+  bool fidelity = false;
+  ArchView view() const {
+    ArchView v{};
+    v.n = topo.n;
+    v.nE = topo.nE;
+    v.bidirectional = topo.bidirectional ? 1 : 0;
+    v.unidirectional = topo.unidirectional ? 1 : 0;
+    v.fidelity = fidelity ? 1 : 0;
+    v.nFid = nFid;
+    v.edges = topo.edges.data();
+    v.incOff = topo.incOff.data();
+    v.inc = topo.inc.data();
+    v.adj = topo.adj.data();
+    v.dist = dist.data();
+    v.distRev = distRev.data();
+    v.c1 = c1.data();
+    v.c2 = c2.data();
+    v.cswap = cswap.data();
+    v.fid = fid.data();
+    return v;
+  }
+};
+
+QMG_API int qemu_arch_create(uint16_t n, const uint16_t* edges, size_t nEdges,
+                             const double* dist, const double* distRev,
+                             qemu_arch** out) {
+  try {
+    auto a = std::make_unique<qemu_arch>();
+    a->topo.build(n, edges, nEdges);
+    const size_t nn = static_cast<size_t>(n) * n;
+    a->dist.assign(dist, dist + nn);
+    a->distRev.assign(distRev, distRev + nn);
+    *out = a.release();
+    return QMG_OK;
+  } catch (const std::exception& e) {
+    return fail(QMG_BAD_ARG, e.what());
+  }
+}
+QMG_API int qemu_arch_set_fidelity(qemu_arch* a, const double* c1,
+                                   const double* c2, const double* cswap,
+                                   const double* fid, uint32_t nFid) {
+  const size_t n = static_cast<size_t>(a->topo.n);
+  a->c1.assign(c1, c1 + n);
+  a->c2.assign(c2, c2 + n * n);
+  a->cswap.assign(cswap, cswap + n * n);
+  a->fid.assign(fid, fid + static_cast<size_t>(nFid) * n * n);
+  a->nFid = static_cast<int>(nFid);
+  a->fidelity = true;
+  return QMG_OK;
+}
+QMG_API void qemu_arch_destroy(qemu_arch* a) { delete a; }
+
+QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
+                             size_t nInstances, const qmg_instance* instances,
+                             qmg_route_result* results, uint32_t poolNodes) {
+  static_assert(sizeof(LayerOut) == sizeof(qmg_layer_result), "layer result");
+  if (const char* msg = checkConfig(*cfg, arch->fidelity)) {
+    return fail(QMG_BAD_ARG, msg);
+  }
+  const ArchView A = arch->view();
+  const CfgView C = toCfgView(*cfg);
+  const int n = A.n;
+  if (poolNodes == 0) {
+    poolNodes = 1U << 16;
+  }
+  uint32_t tableSize = 1;
+  while (tableSize < 2 * poolNodes) {
+    tableSize <<= 1;
+  }
+  const uint32_t recBytes =
+      static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
+  std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8);
+  std::vector<OpenEntry> open(poolNodes);
+  std::vector<uint64_t> table(tableSize, 0);
+  std::vector<int16_t> cur(2 * static_cast<size_t>(n));
+  std::vector<int16_t> ql(2 * static_cast<size_t>(n));
+  std::vector<uint32_t> consMask((n + 31) / 32 + 1);
+  std::vector<Child> ch(kChunk);
+  std::vector<double> lookPen(kChunk / 2 * kLookBlock);
+  std::vector<uint32_t> lookLayers(kLookBlock + 2);
+  uint32_t stamp = 0;
+  for (size_t ii = 0; ii < nInstances; ++ii) {
+    const qmg_instance& in = instances[ii];
+    qmg_route_result& r = results[ii];
+    FlatCircuit fc;
+    fc.build(in.layers.n_layers, in.layers.n_logical, in.layers.gate2q_offsets,
+             reinterpret_cast<const Gate2*>(in.layers.gates2q),
+             in.layers.gate1q_offsets,
+             reinterpret_cast<const Gate1*>(in.layers.gates1q),
+             C.fidelityAware != 0);
+    std::vector<uint16_t> nsw(static_cast<size_t>(fc.maxG) + 1);
+    SearchMem M{};
+    M.pool = reinterpret_cast<uint8_t*>(poolStore.data());
+    M.open = open.data();
+    M.table = table.data();
+    M.curQ = cur.data();
+    M.curL = cur.data() + n;
+    M.nsw = nsw.data();
+    M.poolCap = poolNodes;
+    M.recBytes = recBytes;
+    M.tableMask = tableSize - 1;
+    M.stamp = stamp;
+    M.maxG = fc.maxG;
+    Scratch S{};
+    S.Q = ql.data();
+    S.L = ql.data() + n;
+    S.consMask = consMask.data();
+    S.ch = ch.data();
+    S.lookPen = lookPen.data();
+    S.lookLayers = lookLayers.data();
+    InstView I{};
+    I.circ = fc.view();
+    I.initLoc = in.initial_locations;
+    I.passes = in.bidirectional_passes;
+    I.firstLayer = in.first_layer;
+    I.nRoute = in.n_route_layers;
+    I.layers = reinterpret_cast<LayerOut*>(r.layers);
+    I.swaps = r.swaps;
+    I.swapCap = r.swap_capacity;
+    I.places = reinterpret_cast<uint16_t*>(r.placements);
+    I.placeCap = r.placement_capacity;
+    I.finalQ = r.final_qubits;
+    I.finalL = r.final_locations;
+    I.startL = r.start_locations;
+    I.layerQ = r.layer_qubits;
+    uint32_t summary[4] = {0, 0, 0, 0};
+    uint64_t counters[2] = {0, 0};
+    I.summary = summary;
+    I.counters = counters;
+    Search s(A, C, I, M, S);
+    s.run();
+    stamp = M.stamp;
+    r.n_swaps_total = summary[0];
+    r.n_placements_total = summary[1];
+    r.n_layers_done = summary[2];
+    r.status = static_cast<int32_t>(summary[3]);
+    r.expanded_nodes = counters[0];
+    r.generated_nodes = counters[1];
+  }
+  return QMG_OK;
+}
