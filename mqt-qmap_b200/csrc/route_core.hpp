@@ -240,6 +240,32 @@ QMG_HD Gate2 ldGate(const Gate2* p) {
 #endif
 }
 
+QMG_HD int ctz32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  return __ffs(static_cast<int>(v)) - 1;
+#else
+  return __builtin_ctz(v);
+#endif
+}
+QMG_HD int popc32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  return __popc(v);
+#else
+  return __builtin_popcount(v);
+#endif
+}
+QMG_HD Gate1 ldGate1(const Gate1* p) {
+#if defined(__CUDA_ARCH__)
+  const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p));
+  Gate1 g;
+  g.q = static_cast<uint16_t>(v & 0xffffU);
+  g.mult = static_cast<uint16_t>(v >> 16);
+  return g;
+#else
+  return *p;
+#endif
+}
+
 QMG_HD double gmin(const Group& g, double v) {
   for (int d = Group::W / 2; d > 0; d >>= 1) {
     const double o = g.xorv(v, d);
@@ -694,7 +720,7 @@ struct Search {
     double fixed = root ? 0. : pc.fixed;
     if (root) {
       for (uint32_t i = 0; i < G1; ++i) {
-        const Gate1 e = ldg(gates1 + i);
+        const Gate1 e = ldGate1(gates1 + i);
         fixed += e.mult * ldg(A.c1 + S.L[e.q]);
       }
     }
@@ -733,7 +759,7 @@ struct Search {
       int m1 = 0;
       int m2 = 0;
       for (uint32_t i = 0; i < G1; ++i) {
-        const Gate1 e = ldg(gates1 + i);
+        const Gate1 e = ldGate1(gates1 + i);
         if (e.q == q1) {
           m1 = e.mult;
         }
@@ -749,7 +775,7 @@ struct Search {
     double costHeur = 0.;
     double savings = 0.;
     for (uint32_t i = 0; i < G1; ++i) {
-      const Gate1 e = ldg(gates1 + i);
+      const Gate1 e = ldGate1(gates1 + i);
       const int loc = locAfter(e.q, q1, q2, a, b);
       const double curr = ldg(A.c1 + loc);
       double best = 0.;
@@ -1127,7 +1153,7 @@ struct Search {
           }
         }
         const uint32_t bal = g.ballot(keep);
-        const int add = __builtin_popcount(bal);
+        const int add = popc32(bal);
         if (add == 0) {
           continue;
         }
@@ -1139,7 +1165,7 @@ struct Search {
         }
         if (keep) {
           const int rank =
-              __builtin_popcount(bal & ((1U << g.lane) - 1U));
+              popc32(bal & ((1U << g.lane) - 1U));
           S.ch[cnt + rank].a = static_cast<uint16_t>(ea);
           S.ch[cnt + rank].b = static_cast<uint16_t>(eb);
         }
@@ -1180,7 +1206,7 @@ struct Search {
       const int p = p0 + g.lane;
       const uint32_t bal = g.ballot(p < n && M.curQ[p] == -1);
       if (bal != 0) {
-        return p0 + __builtin_ctz(bal);
+        return p0 + ctz32(bal);
       }
     }
     return -1;
@@ -1211,7 +1237,7 @@ struct Search {
     g.sync();
     if (C.fidelityAware) {
       for (uint32_t i = 0; i < G1; ++i) {
-        const Gate1 e = ldg(gates1 + i);
+        const Gate1 e = ldGate1(gates1 + i);
         if (M.curL[e.q] == -1) {
           const int p = firstFree();
           if (p >= 0) {
@@ -1237,7 +1263,7 @@ struct Search {
           }
           const uint32_t bal = g.ballot(ok);
           if (bal != 0) {
-            const int kk = k0 + __builtin_ctz(bal);
+            const int kk = k0 + ctz32(bal);
             ca = ldg(A.edges + 2 * kk);
             cb = ldg(A.edges + 2 * kk + 1);
             break;

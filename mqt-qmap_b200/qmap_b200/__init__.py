@@ -1,0 +1,5 @@
+"""qmap_b200 - B200-native heuristic router behind QMAP's heuristic-mapper API."""
+from ._abi import QmapError  # noqa: F401
+from .architecture import Architecture, Properties  # noqa: F401
+from .circuit import Circuit, load_qasm, parse_qasm  # noqa: F401
+from .routing import make_config  # noqa: F401
