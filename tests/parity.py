@@ -85,7 +85,9 @@ def compare(out, rr, rel=0.0):
         rs = rr.swap_pairs[b["swap_offset"]: b["swap_offset"] + b["n_swaps"]]
         if not np.array_equal(out.layer_swaps(l), rs):
             return f"layer {l}: swaps differ"
-    if not np.array_equal(out.final_qubits, rr.final_qubits):
+    # (rr.final_qubits is not comparable: routeCircuit rewinds `qubits` through
+    # the SWAPs when it fixes up early single-qubit gates, :461-508)
+    if nl > 0 and not np.array_equal(out.final_qubits, qa[nl - 1]):
         return "final layout differs"
     return ""
 
