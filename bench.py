@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py - A* expanded nodes/s of the heuristic router (BASELINE.json).
+
+Workload at N=1 (configs[1]): examples/qft_16.qasm on IBM QX5, heuristic
+gate_count_max_distance, lookahead gate_count_max_distance x15 (0.75/0.5),
+individual-gates layering; a step routes a batch of B seeded relabellings of the
+circuit (identity initial layout = B different initial layouts).  One step = one
+launch of the routing kernel over the whole batch.
+
+  value     expanded nodes / device time of the kernel (inputs resident in HBM)
+  e2e       the same through qmg_route_batch with host buffers (staging,
+            H2D, kernel, D2H inside the timed region)
+  roofline  algorithmic bytes per launch / kernel time vs measured HBM peak
+  cpu_baseline / --impl reference: the compiled reference (oracle/_ref) on the
+            host cores over a bounded sample of the same batch
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "mqt-qmap_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+QASM = os.path.join(ROOT, "tests", "golden", "circuits", "qft_16.qasm")
+ARCH = os.path.join(ROOT, "tests", "golden", "arch", "ibm_qx5.arch")
+WORKLOAD = "qft_16 on IBM QX5 (16q), lookahead gate_count_max_distance x15, batch of seeded relabellings"
+METRIC = "astar_expanded_nodes_per_sec"
+
+
+def instance_perm(seed: int) -> np.ndarray:
+    return np.random.default_rng(1000003 + seed).permutation(16)
+
+
+def relabel_arrays(c, t, perm):
+    perm = np.asarray(perm, dtype=np.int32)
+    return (np.where(c >= 0, perm[np.maximum(c, 0)], -1).astype(np.int32),
+            perm[t].astype(np.int32))
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the compiled reference on the host cores (test infrastructure)
+# ---------------------------------------------------------------------------
+def _ref_worker(args):
+    seeds, = args
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "mqt-qmap_b200"))
+    from oracle import refapi
+    from qmap_b200 import circuit as qcirc
+    R = refapi.Ref()
+    ra = R.arch_load(ARCH)
+    base = qcirc.load_qasm(QASM)
+    cfg = refapi.make_config(initial_layout="identity", debug=True)
+    exp = gen = swaps = 0
+    t0 = time.perf_counter()
+    search_s = 0.0
+    c0, t0_ = base.gate_arrays()
+    for s in seeds:
+        c, t = relabel_arrays(c0, t0_, instance_perm(s))
+        rr = R.map_gates(ra, 16, c, t, cfg)
+        exp += rr.expanded_nodes
+        gen += rr.generated_nodes
+        swaps += rr.swaps
+        search_s += rr.seconds_per_node * rr.expanded_nodes
+    return exp, gen, swaps, time.perf_counter() - t0, search_s
+
+
+def run_reference(seeds, cores: int):
+    """Routes the given instances with the reference on `cores` processes.
+    Returns (expanded, generated, swaps, wall seconds)."""
+    from concurrent.futures import ProcessPoolExecutor
+    import multiprocessing as mp
+    chunks = [list(seeds[i::cores]) for i in range(cores)]
+    chunks = [c for c in chunks if c]
+    t0 = time.perf_counter()
+    with ProcessPoolExecutor(max_workers=len(chunks), mp_context=mp.get_context("spawn")) as ex:
+        res = list(ex.map(_ref_worker, [(c,) for c in chunks]))
+    wall = time.perf_counter() - t0
+    busy = max(r[3] for r in res)  # excludes process start-up
+    return (sum(r[0] for r in res), sum(r[1] for r in res), sum(r[2] for r in res),
+            busy, wall, sum(r[4] for r in res))
+
+
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index: int):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}",
+                 "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+                 "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(n: int, expanded: int, generated: int) -> float:
+    """per expanded node with b children, R = 4n + 64:
+    R (read parent) + b*R (write children) + 32*b (queue/hash) + 16 (pop)."""
+    R = 4 * n + 64
+    return expanded * (R + 16) + generated * (R + 32)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=16384, help="instances per GPU per step")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = auto)")
+    ap.add_argument("--searches-per-sm", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cores = host_cores()
+    config = {"workload": WORKLOAD, "batch_per_gpu": args.batch,
+              "l2": "flushed between timed steps (512 MiB write)", "parallelism": f"instances x{world}"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        sample = args.cpu_sample or 600 * cores
+        vals = []
+        last = None
+        for step in range(args.warmup + args.steps):
+            seeds = list(range(step * sample, (step + 1) * sample))
+            exp, gen, swaps, busy, wall, search_s = run_reference(seeds, cores)
+            if step >= args.warmup:
+                vals.append((exp, busy))
+            last = (exp, gen, swaps, busy, wall, search_s)
+        tot_e = sum(v[0] for v in vals)
+        tot_t = sum(v[1] for v in vals)
+        v = tot_e / tot_t
+        desc = f"{sample} instances per step on {cores} processes (oracle/_ref = reference sources)"
+        print(json.dumps({
+            "metric": METRIC, "value": v, "unit": "nodes/s", "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": v, "unit": "nodes/s", "cores": cores, "kind": "reference",
+                             "sample": desc,
+                             "search_loop_only_nodes_per_core_s": last[0] / last[5] if last[5] else None},
+            "e2e": {"value": v, "unit": "nodes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "circuits_per_s": sum(1 for _ in range(sample)) * args.steps / tot_t,
+        }))
+        return
+
+    # ---- B200 arm ---------------------------------------------------------
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # before CUDA is initialised in this process (workers are spawned)
+        sample = args.cpu_sample or 2500 * cores
+        exp, gen, swaps, busy, wall, search_s = run_reference(list(range(sample)), cores)
+        cpu_base = {"value": exp / busy, "unit": "nodes/s", "cores": cores, "kind": "reference",
+                    "sample": f"first {sample} instances of the batch, {busy:.1f} s on {cores} processes",
+                    "circuits_per_s": sample / busy,
+                    "search_loop_only_nodes_per_core_s": exp / search_s if search_s else None}
+
+    import torch
+    import torch.distributed as dist
+    from qmap_b200 import _abi, routing
+    from qmap_b200 import circuit as qcirc
+    from qmap_b200.architecture import Architecture
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L = _abi.load()
+    arch = Architecture(device=local_rank).load_coupling_map(ARCH)
+    h = arch.handle
+    n = arch.n_qubits
+    base = qcirc.load_qasm(QASM)
+    cfg = routing.make_config(initial_layout="identity")
+    B = args.batch
+    seeds = range(rank * B, (rank + 1) * B)
+    items = []
+    c0, t0_ = base.gate_arrays()
+    for s in seeds:
+        c, t = relabel_arrays(c0, t0_, instance_perm(s))
+        lc = routing.LayeredCircuit(L, n, c, t, cfg.layering)
+        items.append(routing.RouteItem(lc, np.arange(n, dtype=np.int16)))
+    opts = _abi.QmgRouteOptions()
+    opts.searches_per_sm = args.searches_per_sm
+    bufs = routing.pack(n, items)
+    batch = C.c_void_p()
+    _abi.check(L, L.qmg_batch_create(h, C.byref(cfg), len(items), C.addressof(bufs.inst),
+                                     C.byref(opts), C.byref(batch)))
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    stats = _abi.QmgRouteStats()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        _abi.check(L, L.qmg_batch_run(batch, C.byref(stats)))
+        return stats.kernel_ms
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    kernel_ms = [step() for _ in range(args.steps)]
+    barrier()
+    clocks = sampler.stop()
+    _abi.check(L, L.qmg_batch_fetch(batch, C.addressof(bufs.res)))
+    outs = routing.unpack(bufs)
+    bad = [o.status for o in outs if o.status != 0]
+    if bad:
+        raise RuntimeError(f"{len(bad)} instances failed, first status {bad[0]}")
+    exp = sum(o.expanded_nodes for o in outs)
+    gen = sum(o.generated_nodes for o in outs)
+    swaps = sum(len(o.swaps) for o in outs)
+    L.qmg_batch_destroy(batch)
+
+    # e2e: the C-ABI call a host makes, host buffers in and out
+    e2e_ms = []
+    for i in range(2 + args.steps):
+        b2 = routing.pack(n, items)
+        st2 = _abi.QmgRouteStats()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _abi.check(L, L.qmg_route_batch(h, C.byref(cfg), len(items), C.addressof(b2.inst),
+                                        C.addressof(b2.res), C.byref(opts), C.byref(st2)))
+        dt = time.perf_counter() - t0
+        if i >= 2:
+            e2e_ms.append(1e3 * dt)
+    h2d, d2h = int(st2.h2d_bytes), int(st2.d2h_bytes)
+
+    t_total = sum(kernel_ms) / 1e3
+    t_e2e = sum(e2e_ms) / 1e3
+    red = torch.tensor([t_total, t_e2e], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([exp, gen, swaps, len(items)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    t_total, t_e2e = (float(x) for x in red.tolist())
+    exp_all, gen_all, swaps_all, inst_all = (float(x) for x in cnt.tolist())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    avg_launch_s = (sum(kernel_ms) / len(kernel_ms)) / 1e3
+    abytes = algorithmic_bytes(n, exp, gen)
+    achieved = abytes / avg_launch_s / 1e9
+    out = {
+        "metric": METRIC, "value": exp_all * args.steps / t_total, "unit": "nodes/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+        "clocks": clocks,
+        "e2e": {"value": exp_all * len(e2e_ms) / t_e2e, "unit": "nodes/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": 1e3 * t_e2e / len(e2e_ms),
+                "circuits_per_s": inst_all * len(e2e_ms) / t_e2e},
+        "gpu_launches": args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None,
+                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                     "kernel": "route_kernel", "algorithmic_bytes_per_launch": abytes},
+        "cpu_baseline": cpu_base,
+        "circuits_per_s": inst_all * args.steps / t_total,
+        "expanded_nodes_per_step": exp_all, "generated_nodes_per_step": gen_all,
+        "swaps_per_step": swaps_all, "grid": int(stats.grid), "block": int(stats.block),
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

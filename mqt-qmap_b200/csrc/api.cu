@@ -518,7 +518,8 @@ struct qmg_batch {
   std::vector<uint32_t> nLayers, layerOff, swapCap, swapOff;
   uint64_t totLayers = 0, totSwapCap = 0;
   // device inputs
-  DevBuf<uint32_t> g2Off, g1Off, consOff, next2q, order, ticket;
+  DevBuf<uint32_t> g2Off, g1Off, consOff, twoQ, firstAfter, order, ticket;
+  DevBuf<double> factors;
   DevBuf<Gate2> g2;
   DevBuf<Gate1> g1;
   DevBuf<uint16_t> cons;
@@ -530,7 +531,6 @@ struct qmg_batch {
   DevBuf<uint8_t> pool;
   DevBuf<OpenEntry> open;
   DevBuf<uint64_t> table;
-  DevBuf<int16_t> cur;
   DevBuf<uint16_t> nsw;
   // device outputs
   DevBuf<LayerOut> oLayers;
@@ -575,6 +575,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   auto b = std::make_unique<qmg_batch>();
   b->arch = arch;
   b->cfg = toCfgView(*cfg);
+  if (cfg->nr_lookaheads > (1U << 20)) {
+    return fail(QMG_BAD_ARG, "nr_lookaheads too large");
+  }
   b->nInst = nInst;
   const int n = arch->topo.n;
   b->n = n;
@@ -589,12 +592,13 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     uint32_t nLayers, nLogical, maxG;
   };
   std::vector<CircPos> circs;
-  std::vector<uint32_t> hG2Off, hG1Off, hConsOff, hNext;
+  std::vector<uint32_t> hG2Off, hG1Off, hConsOff, hTwoQ, hFirst;
   std::vector<Gate2> hG2;
   std::vector<Gate1> hG1;
   std::vector<uint16_t> hCons;
   std::vector<uint8_t> hSplit;
   std::vector<uint32_t> circOf(nInst);
+  std::vector<std::pair<size_t, size_t>> twoQPos;
   uint32_t maxG = 1;
   for (size_t i = 0; i < nInst; ++i) {
     const qmg_layers& L = instances[i].layers;
@@ -623,7 +627,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
         }
       }
       CircPos p{hG2Off.size(), hG2.size(),     hG1Off.size(), hG1.size(),
-                hConsOff.size(), hCons.size(), hNext.size(),  fc.nLayers,
+                hConsOff.size(), hCons.size(), hFirst.size(),  fc.nLayers,
                 fc.nLogical,     fc.maxG};
       hG2Off.insert(hG2Off.end(), fc.g2Off.begin(), fc.g2Off.end());
       hG2.insert(hG2.end(), fc.g2.begin(), fc.g2.end());
@@ -631,7 +635,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       hG1.insert(hG1.end(), fc.g1.begin(), fc.g1.end());
       hConsOff.insert(hConsOff.end(), fc.consOff.begin(), fc.consOff.end());
       hCons.insert(hCons.end(), fc.cons.begin(), fc.cons.end());
-      hNext.insert(hNext.end(), fc.next2q.begin(), fc.next2q.end());
+      hFirst.insert(hFirst.end(), fc.firstAfter.begin(), fc.firstAfter.end());
+      twoQPos.push_back({hTwoQ.size(), fc.twoQ.size()});
+      hTwoQ.insert(hTwoQ.end(), fc.twoQ.begin(), fc.twoQ.end());
       hSplit.insert(hSplit.end(), fc.splittable.begin(), fc.splittable.end());
       maxG = std::max(maxG, fc.maxG);
       it = seen.emplace(key, static_cast<uint32_t>(circs.size())).first;
@@ -645,11 +651,18 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->g1.upload(hG1, s);
   b->consOff.upload(hConsOff, s);
   b->cons.upload(hCons, s);
-  b->next2q.upload(hNext, s);
+  b->twoQ.upload(hTwoQ, s);
+  b->firstAfter.upload(hFirst, s);
+  {
+    const std::vector<double> f = lookaheadFactors(*cfg, 1U << 20);
+    b->factors.upload(f, s);
+    b->cfg.factors = b->factors.p;
+    b->cfg.nFactors = static_cast<uint32_t>(f.size());
+  }
   b->splittable.upload(hSplit, s);
   b->h2dBytes = hG2Off.size() * 4 + hG2.size() * 8 + hG1Off.size() * 4 +
                 hG1.size() * 4 + hConsOff.size() * 4 + hCons.size() * 2 +
-                hNext.size() * 4 + hSplit.size();
+                (hTwoQ.size() + hFirst.size()) * 4 + hSplit.size();
 
   // ---- per-instance inputs / outputs
   b->nLayers.resize(nInst);
@@ -711,7 +724,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.circ.g1 = b->g1.p + c.g1;
     I.circ.consOff = b->consOff.p + c.consOff;
     I.circ.cons = b->cons.p + c.cons;
-    I.circ.next2q = b->next2q.p + c.layer;
+    I.circ.twoQ = b->twoQ.p + twoQPos[circOf[i]].first;
+    I.circ.nTwoQ = static_cast<uint32_t>(twoQPos[circOf[i]].second);
+    I.circ.firstAfter = b->firstAfter.p + c.layer;
     I.circ.splittable = b->splittable.p + c.layer;
     // a null initial layout means "all unplaced"; the staged copy holds -1s
     I.initLoc = b->initLoc.p + i * n;
@@ -796,7 +811,6 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   CU(cudaMemsetAsync(b->table.p, 0,
                      static_cast<size_t>(nWarps) * tableSize * sizeof(uint64_t),
                      s));
-  b->cur.alloc(static_cast<size_t>(nWarps) * 2 * n);
   b->nsw.alloc(static_cast<size_t>(nWarps) * 32 * maxG);
   std::vector<SearchMem> hMem(nWarps);
   for (uint32_t w = 0; w < nWarps; ++w) {
@@ -804,8 +818,6 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     M.pool = b->pool.p + static_cast<size_t>(w) * poolNodes * recBytes;
     M.open = b->open.p + static_cast<size_t>(w) * poolNodes;
     M.table = b->table.p + static_cast<size_t>(w) * tableSize;
-    M.curQ = b->cur.p + static_cast<size_t>(w) * 2 * n;
-    M.curL = M.curQ + n;
     M.nsw = b->nsw.p + static_cast<size_t>(w) * 32 * maxG;
     M.poolCap = poolNodes;
     M.recBytes = recBytes;

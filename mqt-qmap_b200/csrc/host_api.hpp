@@ -6,6 +6,7 @@
 #include <exception>
 #include <memory>
 #include <string>
+#include <vector>
 
 #include "../../include/qmap_b200.h"
 #include "layers.hpp"
@@ -18,6 +19,16 @@ inline std::string& lastError() {
 inline int fail(int code, const std::string& msg) {
   lastError() = msg;
   return code;
+}
+// factor table of updateLookaheadPenalty (:1361,:1381)
+inline std::vector<double> lookaheadFactors(const qmg_config& c, size_t cap) {
+  std::vector<double> f;
+  double v = c.first_lookahead_factor;
+  for (size_t i = 0; i < c.nr_lookaheads && i < cap; ++i) {
+    f.push_back(v);
+    v *= c.lookahead_factor;
+  }
+  return f;
 }
 inline CfgView toCfgView(const qmg_config& c) {
   CfgView v{};

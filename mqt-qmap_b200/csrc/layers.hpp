@@ -236,7 +236,7 @@ struct LayeredCircuit {
 // CSR form of a layered circuit (what CircView points into)
 struct FlatCircuit {
   uint32_t nLayers = 0, nLogical = 0;
-  std::vector<uint32_t> g2Off, g1Off, consOff, next2q;
+  std::vector<uint32_t> g2Off, g1Off, consOff, twoQ, firstAfter;
   std::vector<Gate2> g2;
   std::vector<Gate1> g1;
   std::vector<uint16_t> cons;
@@ -261,14 +261,14 @@ struct FlatCircuit {
     }
     consOff.assign(1, 0);
     cons.clear();
-    next2q.assign(nL, kNone);
     splittable.assign(nL, 0);
-    uint32_t next = kNone;
-    for (uint32_t l = nL; l-- > 0;) {
-      next2q[l] = next;
+    twoQ.clear();
+    firstAfter.assign(nL, 0);
+    for (uint32_t l = 0; l < nL; ++l) {
       if (g2Off[l + 1] > g2Off[l]) {
-        next = l;
+        twoQ.push_back(l);
       }
+      firstAfter[l] = static_cast<uint32_t>(twoQ.size());
     }
     for (uint32_t l = 0; l < nL; ++l) {
       std::set<uint16_t> c, a1, a2;
@@ -326,7 +326,9 @@ struct FlatCircuit {
     v.g1 = g1.data();
     v.consOff = consOff.data();
     v.cons = cons.data();
-    v.next2q = next2q.data();
+    v.twoQ = twoQ.data();
+    v.firstAfter = firstAfter.data();
+    v.nTwoQ = static_cast<uint32_t>(twoQ.size());
     v.splittable = splittable.data();
     return v;
   }

@@ -17,7 +17,7 @@ constexpr int kWarpsPerCta = 4;
 
 struct SmemLayout {
   uint32_t bytesPerWarp;
-  uint32_t offL, offMask, offCh, offLookPen, offLookLayers;
+  uint32_t offL, offCurQ, offCurL, offMask, offCh, offLookPen;
 };
 
 inline SmemLayout smemLayout(int n) {
@@ -27,14 +27,16 @@ inline SmemLayout smemLayout(int n) {
   o += al(static_cast<uint32_t>(n) * 2U);  // Q
   s.offL = o;
   o += al(static_cast<uint32_t>(n) * 2U);
+  s.offCurQ = o;
+  o += al(static_cast<uint32_t>(n) * 2U);
+  s.offCurL = o;
+  o += al(static_cast<uint32_t>(n) * 2U);
   s.offMask = o;
   o += al((static_cast<uint32_t>(n) + 31U) / 32U * 4U + 4U);
   s.offCh = o;
   o += al(static_cast<uint32_t>(sizeof(Child)) * kChunk);
   s.offLookPen = o;
   o += al(8U * (kChunk / 2) * kLookBlock);
-  s.offLookLayers = o;
-  o += al(4U * (kLookBlock + 2));
   s.bytesPerWarp = o;
   return s;
 }
@@ -52,10 +54,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
   Scratch S;
   S.Q = reinterpret_cast<int16_t*>(base);
   S.L = reinterpret_cast<int16_t*>(base + sl.offL);
+  S.curQ = reinterpret_cast<int16_t*>(base + sl.offCurQ);
+  S.curL = reinterpret_cast<int16_t*>(base + sl.offCurL);
   S.consMask = reinterpret_cast<uint32_t*>(base + sl.offMask);
   S.ch = reinterpret_cast<Child*>(base + sl.offCh);
   S.lookPen = reinterpret_cast<double*>(base + sl.offLookPen);
-  S.lookLayers = reinterpret_cast<uint32_t*>(base + sl.offLookLayers);
   SearchMem M = mem[gw];
   for (;;) {
     uint32_t t = 0;

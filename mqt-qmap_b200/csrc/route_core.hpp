@@ -37,6 +37,7 @@ constexpr double kTol = 1e-6;          // HeuristicMapper.hpp:463,473
 constexpr uint32_t kNone = 0xFFFFFFFFU;
 constexpr int kChunk = 32;    // children scored per pass
 constexpr int kLookBlock = 16; // lookahead layers scored per pass
+constexpr uint32_t kScanMax = 96;  // open-list length up to which push() scans
 
 enum Status : int32_t {
   ST_OK = 0,
@@ -79,6 +80,10 @@ struct CfgView {
   uint64_t splitLimit;
   int32_t autoSplit;
   int32_t tight, fidelityAware;
+  // factors[i] = firstFactor * factor^i built by repeated multiplication as
+  // updateLookaheadPenalty does (:1361,:1381); min(nrLookaheads, cap) entries
+  const double* factors;
+  uint32_t nFactors;
 };
 
 // layers of one circuit (Mapper::createLayers, src/sc/Mapper.cpp:138-281)
@@ -90,7 +95,12 @@ struct CircView {
   const Gate1* g1;
   const uint32_t* consOff;  // getConsideredQubits(layer), ascending
   const uint16_t* cons;
-  const uint32_t* next2q;   // Mapper::getNextLayer
+  // Mapper::getNextLayer (src/sc/Mapper.cpp:437-448) in closed form: twoQ is
+  // the ascending list of layers holding a 2q gate, firstAfter[l] the index in
+  // twoQ of the first such layer > l
+  const uint32_t* twoQ;
+  const uint32_t* firstAfter;
+  uint32_t nTwoQ;
   const uint8_t* splittable;  // Mapper::isLayerSplittable
 };
 
@@ -134,8 +144,9 @@ struct NodeHdr {  // 72 bytes, followed by qubits[n], locations[n]
 };
 static_assert(sizeof(NodeHdr) == 72, "NodeHdr layout");
 
-struct OpenEntry {
+struct OpenEntry {  // 32 bytes
   double f, h2;
+  uint64_t hash;
   uint32_t idx;
   uint16_t nValid;
   uint16_t valid;
@@ -155,8 +166,6 @@ struct SearchMem {
   uint8_t* pool;
   OpenEntry* open;
   uint64_t* table;
-  int16_t* curQ;
-  int16_t* curL;
   uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
   uint32_t poolCap, recBytes, tableMask, stamp;
   uint32_t maxG;
@@ -164,25 +173,31 @@ struct SearchMem {
 
 // per resident search, in shared memory (device) / plain arrays (host)
 struct Scratch {
-  int16_t* Q;
+  int16_t* Q;     // layout of the node being expanded
   int16_t* L;
+  int16_t* curQ;  // Mapper::qubits / Mapper::locations of the instance
+  int16_t* curL;
   uint32_t* consMask;
   Child* ch;
-  double* lookPen;       // (kChunk / 2) * kLookBlock
-  uint32_t* lookLayers;  // kLookBlock + 2
-};
+  double* lookPen;       // (kChunk / 2) * kLookBlock; also output staging
+  };
 
-QMG_HD uint64_t mix64(uint64_t x) {
-  x += 0x9E3779B97F4A7C15ULL;
-  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
-  x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
-  return x ^ (x >> 31);
+QMG_HD uint32_t mix32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352dU;
+  x ^= x >> 15;
+  x *= 0x846ca68bU;
+  x ^= x >> 16;
+  return x;
 }
-// layout hash: sum over physical qubits of mix(p, qubits[p]); updated
-// incrementally per SWAP.  Also reported as qmg_layer_result.layout_hash.
+// layout hash: sum over physical qubits of a 64-bit mix of (p, qubits[p]);
+// updated incrementally per SWAP.  Also reported as
+// qmg_layer_result.layout_hash.
 QMG_HD uint64_t cellHash(int p, int q) {
-  return mix64((static_cast<uint64_t>(static_cast<uint32_t>(p)) << 16) |
-               static_cast<uint16_t>(q));
+  const uint32_t x = (static_cast<uint32_t>(p) << 16) | static_cast<uint16_t>(q);
+  const uint32_t lo = mix32(x + 0x9E3779B9U);
+  const uint32_t hi = mix32(x ^ 0x85EBCA6BU);
+  return (static_cast<uint64_t>(hi) << 32) | lo;
 }
 
 // ---------------------------------------------------------------------------
@@ -320,7 +335,13 @@ struct Search {
   const uint16_t* cons = nullptr;
   uint32_t nCons = 0;
   uint32_t fidK = 0;  // table index |considered|-1 (kNone => cost 0)
-  uint32_t nLook = 0;
+  uint32_t nLook = 0;  // lookahead layers available from this layer
+  const uint32_t* lookLayers = nullptr;
+  int16_t* pQ = nullptr;  // layout the scoring functions read
+  int16_t* pL = nullptr;
+  bool tableMode = false;
+  bool maskReady = false;
+  uint64_t totExpanded = 0, totGenerated = 0;
 
   QMG_HD Search(const ArchView& a, const CfgView& c, const InstView& i,
                 SearchMem& m, Scratch& s)
@@ -380,7 +401,7 @@ struct Search {
     if (q == q2) {
       return a;
     }
-    return S.L[q];
+    return pL[q];
   }
 
   // updateSharedSwaps :975-1053 (state before the swap)
@@ -404,8 +425,8 @@ struct Search {
       }
     }
     if (p1 != q1 && p2 != q2 && p1 != q2) {
-      const int physQ3 = S.L[p1];
-      const int physQ4 = S.L[p2];
+      const int physQ3 = pL[p1];
+      const int physQ4 = pL[p2];
       double e1b, e1n, e2b, e2n;
       if (C.fidelityAware) {
         e1b = fmin(fidDist(a, physQ3, 0), fidDist(physQ3, a, 0));
@@ -463,8 +484,8 @@ struct Search {
   QMG_HD void scoreGateCount(int a, int b, const ParentCosts& pc, Child& out,
                              uint16_t* nsw) const {
     const bool root = (a == b);
-    const int q1 = root ? -2 : S.Q[a];
-    const int q2 = root ? -2 : S.Q[b];
+    const int q1 = root ? -2 : pQ[a];
+    const int q2 = root ? -2 : pQ[b];
     out.a = static_cast<uint16_t>(a);
     out.b = static_cast<uint16_t>(b);
     const int h = C.heuristic;
@@ -599,7 +620,7 @@ struct Search {
         const int loc = firstFree ? loc2 : loc1;
         double mn = DBL_MAX;
         for (int j = 0; j < n; ++j) {
-          const int qj = (j == a) ? q2 : ((j == b) ? q1 : S.Q[j]);
+          const int qj = (j == a) ? q2 : ((j == b) ? q1 : pQ[j]);
           if (qj != -1) {
             continue;
           }
@@ -632,10 +653,11 @@ struct Search {
 
   // updateLookaheadPenalty :1356-1385 for the cnt children in S.ch (or the
   // root when rootOnly).  Items (child, lookahead layer) are spread over the
-  // lanes; the factor-weighted sum is then accumulated per child in layer
-  // order with the reference's operation order.
+  // lanes (16 lookahead layers x 16 children per pass); the factor-weighted
+  // sum is then accumulated per child in layer order with the reference's
+  // operation order (acc += factor_i * penalty_i).
   QMG_HD void scoreLookahead(int cnt, bool rootOnly) {
-    if (C.lookahead == 0) {
+    if (C.lookahead == 0 || nLook == 0) {
       for (int c = g.lane; c < cnt; c += Group::W) {
         S.ch[c].look = 0.;
       }
@@ -645,58 +667,40 @@ struct Search {
     constexpr int kHalf = kChunk / 2;
     for (int c0 = 0; c0 < cnt; c0 += kHalf) {
       const int nc = (cnt - c0) < kHalf ? (cnt - c0) : kHalf;
-      uint32_t nextLayer = ldg(I.circ.next2q + layer);
-      double factor = C.firstFactor;
       for (int c = g.lane; c < nc; c += Group::W) {
         S.ch[c0 + c].look = 0.;
       }
-      uint32_t done = 0;
-      while (done < C.nrLookaheads && nextLayer != kNone) {
-        // collect the next block of lookahead layers
-        uint32_t nb = 0;
-        if (g.lane == 0) {
-          uint32_t nl = nextLayer;
-          while (nb < static_cast<uint32_t>(kLookBlock) &&
-                 done + nb < C.nrLookaheads && nl != kNone) {
-            S.lookLayers[nb++] = nl;
-            nl = ldg(I.circ.next2q + nl);
-          }
-          S.lookLayers[kLookBlock] = nl;
-          S.lookLayers[kLookBlock + 1] = nb;
-        }
+      for (uint32_t s0 = 0; s0 < nLook; s0 += kLookBlock) {
+        const uint32_t nb =
+            (nLook - s0) < static_cast<uint32_t>(kLookBlock)
+                ? (nLook - s0)
+                : static_cast<uint32_t>(kLookBlock);
         g.sync();
-        nb = S.lookLayers[kLookBlock + 1];
-        nextLayer = S.lookLayers[kLookBlock];
-        const int items = nc * static_cast<int>(nb);
-        for (int it = g.lane; it < items; it += Group::W) {
-          const int c = it / static_cast<int>(nb);
-          const int s = it - c * static_cast<int>(nb);
-          const Child& ch = S.ch[c0 + c];
+        for (int it = g.lane; it < nc * kLookBlock; it += Group::W) {
+          const int c = it / kLookBlock;
+          const uint32_t sl = static_cast<uint32_t>(it % kLookBlock);
+          if (sl >= nb) {
+            continue;
+          }
           int a = -1, b = -1, q1 = -2, q2 = -2;
           if (!rootOnly) {
+            const Child& ch = S.ch[c0 + c];
             a = ch.a;
             b = ch.b;
-            q1 = S.Q[a];
-            q2 = S.Q[b];
+            q1 = pQ[a];
+            q2 = pQ[b];
           }
-          S.lookPen[c * kLookBlock + s] =
-              lookaheadPenalty(S.lookLayers[s], a, b, q1, q2);
+          S.lookPen[it] =
+              lookaheadPenalty(ldg(lookLayers + s0 + sl), a, b, q1, q2);
         }
         g.sync();
         for (int c = g.lane; c < nc; c += Group::W) {
           double acc = S.ch[c0 + c].look;
-          double f = factor;
-          for (uint32_t s = 0; s < nb; ++s) {
-            acc += f * S.lookPen[c * kLookBlock + s];
-            f *= C.factor;
+          for (uint32_t sl = 0; sl < nb; ++sl) {
+            acc += ldg(C.factors + s0 + sl) * S.lookPen[c * kLookBlock + sl];
           }
           S.ch[c0 + c].look = acc;
         }
-        for (uint32_t s = 0; s < nb; ++s) {
-          factor *= C.factor;
-        }
-        done += nb;
-        g.sync();
       }
     }
     g.sync();
@@ -712,8 +716,8 @@ struct Search {
   // ------------------------------------------------------------------------
   QMG_HD void scoreFidelity(int a, int b, const ParentCosts& pc, Child& out) {
     const bool root = (a == b);
-    const int q1 = root ? -2 : S.Q[a];
-    const int q2 = root ? -2 : S.Q[b];
+    const int q1 = root ? -2 : pQ[a];
+    const int q2 = root ? -2 : pQ[b];
     if (root) {
       a = b = -1;
     }
@@ -721,7 +725,7 @@ struct Search {
     if (root) {
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
-        fixed += e.mult * ldg(A.c1 + S.L[e.q]);
+        fixed += e.mult * ldg(A.c1 + pL[e.q]);
       }
     }
     uint32_t nValid = 0;
@@ -743,8 +747,8 @@ struct Search {
       if (!touched) {
         continue;
       }
-      const int o3 = S.L[e.q1];
-      const int o4 = S.L[e.q2];
+      const int o3 = pL[e.q1];
+      const int o4 = pL[e.q2];
       const bool before = adjU(o3, o4);
       if (valid && !before) {
         fixed += e.fwd * ldg(A.c2 + p3 * n + p4) +
@@ -827,7 +831,7 @@ struct Search {
   }
 
   // ------------------------------------------------------------------------
-  // open list: UniquePriorityQueue semantics on (open[], table[], pool)
+  // open list: UniquePriorityQueue semantics on (open[], pool, table[])
   // ------------------------------------------------------------------------
   // node order, HeuristicMapper.hpp:452-483, first four keys.
   // returns -1 if x has priority, +1 if y has priority, 0 if tied
@@ -846,6 +850,20 @@ struct Search {
     }
     return 0;
   }
+  // 4 consecutive qubits[] entries as one integer whose unsigned order is the
+  // lexicographic order of the (signed) entries
+  QMG_HD uint64_t lexChunk(const int16_t* q, int i0) const {
+    uint64_t k = 0;
+    for (int t = 0; t < 4; ++t) {
+      const int i = i0 + t;
+      const uint32_t v =
+          i < n ? (static_cast<uint32_t>(static_cast<int32_t>(q[i]) + 0x8000) &
+                   0xffffU)
+                : 0U;
+      k = (k << 16) | v;
+    }
+    return k;
+  }
   // full order incl. the lexicographic tie-break (:438-450, :482): among
   // tied nodes the lexicographically LARGEST qubits[] is on top
   QMG_HD bool hasPriority(const OpenEntry& x, const OpenEntry& y) const {
@@ -858,22 +876,42 @@ struct Search {
     }
     const int16_t* qx = nodeQ(x.idx);
     const int16_t* qy = nodeQ(y.idx);
-    for (int i = 0; i < n; ++i) {
-      const int16_t vx = qx[i];
-      const int16_t vy = qy[i];
-      if (vx != vy) {
-        return vx > vy;
+    for (int i = 0; i < n; i += 4) {
+      const uint64_t kx = lexChunk(qx, i);
+      const uint64_t ky = lexChunk(qy, i);
+      if (kx != ky) {
+        return kx > ky;
       }
     }
     return false;
   }
 
-  // position of the top of the open list (group-uniform result)
+  QMG_HD uint32_t gmaxU32(uint32_t v) const {
+    for (int d = Group::W / 2; d > 0; d >>= 1) {
+      const uint32_t o = g.xorv(v, d);
+      v = o > v ? o : v;
+    }
+    return v;
+  }
+  QMG_HD uint64_t gmaxU64(uint64_t v) const {
+    for (int d = Group::W / 2; d > 0; d >>= 1) {
+      const uint64_t o = g.xorv(v, d);
+      v = o > v ? o : v;
+    }
+    return v;
+  }
+
+  // position of the top of the open list (group-uniform result).  Every lane
+  // reduces its strided share with the pairwise order; the lanes' winners are
+  // then narrowed key by key (cost band, validity, heuristic band, valid-gate
+  // count, lexicographic layout), which selects the same node as the pairwise
+  // order whenever that order is a strict weak order.
   QMG_HD uint32_t topPos() const {
     OpenEntry best;
     uint32_t bestPos = kNone;
-    best.f = 0.;
-    best.h2 = 0.;
+    best.f = DBL_MAX;
+    best.h2 = DBL_MAX;
+    best.hash = 0;
     best.idx = kNone;
     best.nValid = 0;
     best.valid = 0;
@@ -884,22 +922,33 @@ struct Search {
         bestPos = i;
       }
     }
-    for (int d = Group::W / 2; d > 0; d >>= 1) {
-      OpenEntry o;
-      o.f = g.xorv(best.f, d);
-      o.h2 = g.xorv(best.h2, d);
-      o.idx = g.xorv(best.idx, d);
-      const uint32_t pk = g.xorv(
-          (static_cast<uint32_t>(best.nValid) << 16) | best.valid, d);
-      o.nValid = static_cast<uint16_t>(pk >> 16);
-      o.valid = static_cast<uint16_t>(pk & 0xffffU);
-      const uint32_t op = g.xorv(bestPos, d);
-      if (op != kNone && (bestPos == kNone || hasPriority(o, best))) {
-        best = o;
-        bestPos = op;
+    if (Group::W == 1) {
+      return bestPos;
+    }
+    bool cand = bestPos != kNone;
+    const double fmn = gmin(g, cand ? best.f : DBL_MAX);
+    cand = cand && !(fabs(best.f - fmn) > kTol);
+    uint32_t m = g.ballot(cand);
+    if (popc32(m) > 1) {
+      const uint32_t mv = g.ballot(cand && best.valid != 0);
+      if (mv != 0) {
+        cand = cand && best.valid != 0;
+      }
+      const double hmn = gmin(g, cand ? best.h2 : DBL_MAX);
+      cand = cand && !(fabs(best.h2 - hmn) > kTol);
+      const uint32_t nv = gmaxU32(cand ? best.nValid + 1U : 0U);
+      cand = cand && (best.nValid + 1U == nv);
+      m = g.ballot(cand);
+      const int16_t* q = cand ? nodeQ(best.idx) : nullptr;
+      for (int i = 0; i < n && popc32(m) > 1; i += 4) {
+        const uint64_t k = cand ? lexChunk(q, i) : 0ULL;
+        const uint64_t kmx = gmaxU64(k);
+        cand = cand && k == kmx;
+        m = g.ballot(cand);
       }
     }
-    return bestPos;
+    const int src = ctz32(m);
+    return g.bcast(bestPos, src);
   }
 
   QMG_HD void removeOpen(uint32_t pos) {
@@ -918,7 +967,7 @@ struct Search {
     g.sync();
   }
 
-  // write a node record: parent layout (S.Q/S.L) with the child's swap
+  // write a node record: parent layout (pQ/pL) with the child's swap
   QMG_HD void writeNode(uint32_t idx, const Child& ch, uint32_t parentIdx,
                         uint32_t depth, uint32_t id, uint32_t openPos,
                         bool root) {
@@ -926,11 +975,11 @@ struct Search {
     int16_t* l = nodeL(idx);
     const int a = ch.a;
     const int b = ch.b;
-    const int q1 = root ? -2 : S.Q[a];
-    const int q2 = root ? -2 : S.Q[b];
+    const int q1 = root ? -2 : pQ[a];
+    const int q2 = root ? -2 : pQ[b];
     for (int i = g.lane; i < n; i += Group::W) {
-      int16_t vq = S.Q[i];
-      int16_t vl = S.L[i];
+      int16_t vq = pQ[i];
+      int16_t vl = pL[i];
       if (!root) {
         if (i == a) {
           vq = static_cast<int16_t>(q2);
@@ -970,6 +1019,7 @@ struct Search {
     OpenEntry e;
     e.f = ch.fixed + ch.rev + ch.heur + ch.look;  // Node::getTotalCost
     e.h2 = ch.heur + ch.look;
+    e.hash = ch.hash;
     e.idx = idx;
     e.nValid = ch.nValid;
     e.valid = ch.valid;
@@ -985,12 +1035,12 @@ struct Search {
     for (int i0 = 0; i0 < n; i0 += Group::W) {
       const int i = i0 + g.lane;
       if (i < n) {
-        int16_t v = S.Q[i];
+        int16_t v = pQ[i];
         if (!root) {
           if (i == a) {
-            v = S.Q[b];
+            v = pQ[b];
           } else if (i == b) {
-            v = S.Q[a];
+            v = pQ[a];
           }
         }
         diff = diff || (q[i] != v);
@@ -1002,27 +1052,69 @@ struct Search {
     return true;
   }
 
+  // switch from scanning the open list to the layout-keyed hash table
+  QMG_HD void buildTable() {
+    g.sync();
+    if (g.lane == 0) {
+      for (uint32_t i = 0; i < nOpen; ++i) {
+        const OpenEntry e = M.open[i];
+        uint32_t slot = static_cast<uint32_t>(e.hash ^ (e.hash >> 32)) &
+                        M.tableMask;
+        while (static_cast<uint32_t>(M.table[slot] >> 32) == M.stamp) {
+          slot = (slot + 1) & M.tableMask;
+        }
+        M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | e.idx;
+      }
+    }
+    tableMode = true;
+    g.sync();
+  }
+
   // UniquePriorityQueue::push :59-82.  Group-uniform.  Returns false when the
-  // node pool is exhausted.
+  // node pool is exhausted.  Only nodes in the open list take part in the
+  // layout identity (pop erases the membership, :84-93), so short open lists
+  // are scanned directly; longer ones are indexed by the hash table.
   QMG_HD bool push(const Child& ch, uint32_t parentIdx, uint32_t depth,
                    bool root) {
     const uint32_t id = nextId++;
     const uint64_t h = ch.hash;
-    uint32_t slot = static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
-    uint32_t found = kNone;
-    for (;;) {
-      const uint64_t e = M.table[slot];
-      if (static_cast<uint32_t>(e >> 32) != M.stamp) {
-        break;  // free slot
-      }
-      const uint32_t idx = static_cast<uint32_t>(e);
-      if (hdr(idx)->hash == h && sameLayout(idx, ch, root)) {
-        found = idx;
-        break;
-      }
-      slot = (slot + 1) & M.tableMask;
+    uint32_t found = kNone;  // pool index of an OPEN node with this layout
+    uint32_t slot = 0;
+    if (!tableMode && nOpen > kScanMax) {
+      buildTable();
     }
-    if (found != kNone && (hdr(found)->flags & 2U) != 0) {
+    if (!tableMode) {
+      for (uint32_t i0 = 0; i0 < nOpen && found == kNone; i0 += Group::W) {
+        const uint32_t i = i0 + g.lane;
+        uint32_t m = g.ballot(i < nOpen && M.open[i].hash == h);
+        while (m != 0 && found == kNone) {
+          const int src = ctz32(m);
+          m &= m - 1;
+          const uint32_t idx = M.open[i0 + src].idx;
+          if (sameLayout(idx, ch, root)) {
+            found = idx;
+          }
+        }
+      }
+    } else {
+      slot = static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
+      for (;;) {
+        const uint64_t e = M.table[slot];
+        if (static_cast<uint32_t>(e >> 32) != M.stamp) {
+          break;  // free slot
+        }
+        const uint32_t idx = static_cast<uint32_t>(e);
+        if (hdr(idx)->hash == h && sameLayout(idx, ch, root)) {
+          found = idx;
+          break;
+        }
+        slot = (slot + 1) & M.tableMask;
+      }
+      if (found != kNone && (hdr(found)->flags & 2U) == 0) {
+        found = kNone;  // closed: the slot is re-pointed to the new node below
+      }
+    }
+    if (found != kNone) {
       // layout is in the open list: keep the better one (:63-79)
       const uint32_t pos = hdr(found)->openPos;
       const OpenEntry ex = M.open[pos];
@@ -1047,7 +1139,9 @@ struct Search {
     writeNode(idx, ch, parentIdx, depth, id, pos, root);
     if (g.lane == 0) {
       M.open[pos] = entryOf(ch, idx);
-      M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | idx;
+      if (tableMode) {
+        M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | idx;
+      }
     }
     g.sync();
     return true;
@@ -1086,8 +1180,8 @@ struct Search {
     for (int c = g.lane; c < cnt; c += Group::W) {
       const int a = S.ch[c].a;
       const int b = S.ch[c].b;
-      const int q1 = S.Q[a];
-      const int q2 = S.Q[b];
+      const int q1 = pQ[a];
+      const int q2 = pQ[b];
       S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
                      cellHash(a, q2) + cellHash(b, q1);
     }
@@ -1108,12 +1202,17 @@ struct Search {
   // only from the smallest considered qubit of the pair and only on the
   // smaller of the (up to two) directed edges between them.
   QMG_HD bool expand(uint32_t parentIdx) {
+    if (!maskReady) {
+      buildMask();
+    }
     // stage the parent
+    pQ = S.Q;
+    pL = S.L;
     const int16_t* pq = nodeQ(parentIdx);
     const int16_t* pl = nodeL(parentIdx);
     for (int i = g.lane; i < n; i += Group::W) {
-      S.Q[i] = pq[i];
-      S.L[i] = pl[i];
+      pQ[i] = pq[i];
+      pL[i] = pl[i];
     }
     const NodeHdr* ph = hdr(parentIdx);
     ParentCosts pc;
@@ -1125,7 +1224,7 @@ struct Search {
     int cnt = 0;
     for (uint32_t ci = 0; ci < nCons; ++ci) {
       const int q = ldg(cons + ci);
-      const int p = S.L[q];
+      const int p = pL[q];
       if (p < 0) {
         continue;
       }
@@ -1140,8 +1239,8 @@ struct Search {
           const uint32_t e = ldg(A.inc + k);
           ea = ldg(A.edges + 2 * e);
           eb = ldg(A.edges + 2 * e + 1);
-          const int qa = S.Q[ea];
-          const int qb = S.Q[eb];
+          const int qa = pQ[ea];
+          const int qb = pQ[eb];
           if (qa == -1 || qb == -1) {
             keep = true;
           } else {
@@ -1181,15 +1280,15 @@ struct Search {
   }
 
   // ------------------------------------------------------------------------
-  // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on M.curQ / M.curL
+  // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on S.curQ / S.curL
   // ------------------------------------------------------------------------
   uint32_t nPlace = 0;  // running count into I.places
   bool record = false;
 
   QMG_HD void place(int logical, int phys) {
     if (g.lane == 0) {
-      M.curQ[phys] = static_cast<int16_t>(logical);
-      M.curL[logical] = static_cast<int16_t>(phys);
+      S.curQ[phys] = static_cast<int16_t>(logical);
+      S.curL[logical] = static_cast<int16_t>(phys);
       if (record && I.places != nullptr && nPlace < I.placeCap) {
         I.places[2 * nPlace] = static_cast<uint16_t>(logical);
         I.places[2 * nPlace + 1] = static_cast<uint16_t>(phys);
@@ -1204,7 +1303,7 @@ struct Search {
   QMG_HD int firstFree() const {
     for (int p0 = 0; p0 < n; p0 += Group::W) {
       const int p = p0 + g.lane;
-      const uint32_t bal = g.ballot(p < n && M.curQ[p] == -1);
+      const uint32_t bal = g.ballot(p < n && S.curQ[p] == -1);
       if (bal != 0) {
         return p0 + ctz32(bal);
       }
@@ -1213,11 +1312,11 @@ struct Search {
   }
 
   QMG_HD bool mapToMinDistance(int source, int target) {
-    const int src = M.curL[source];
+    const int src = S.curL[source];
     double best = DBL_MAX;
     uint32_t pos = kNone;
     for (int i = g.lane; i < n; i += Group::W) {
-      if (M.curQ[i] == -1) {
+      if (S.curQ[i] == -1) {
         const double d = dRev(src, i);
         if (d < best) {
           best = d;
@@ -1238,7 +1337,7 @@ struct Search {
     if (C.fidelityAware) {
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
-        if (M.curL[e.q] == -1) {
+        if (S.curL[e.q] == -1) {
           const int p = firstFree();
           if (p >= 0) {
             place(e.q, p);
@@ -1248,8 +1347,8 @@ struct Search {
     }
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
-      const int l1 = M.curL[e.q1];
-      const int l2 = M.curL[e.q2];
+      const int l1 = S.curL[e.q1];
+      const int l2 = S.curL[e.q2];
       if (l1 == -1 && l2 == -1) {
         // first coupling edge (ascending) with both ends free
         int ca = -1;
@@ -1258,8 +1357,8 @@ struct Search {
           const int k = k0 + g.lane;
           bool ok = false;
           if (k < A.nE) {
-            ok = M.curQ[ldg(A.edges + 2 * k)] == -1 &&
-                 M.curQ[ldg(A.edges + 2 * k + 1)] == -1;
+            ok = S.curQ[ldg(A.edges + 2 * k)] == -1 &&
+                 S.curQ[ldg(A.edges + 2 * k + 1)] == -1;
           }
           const uint32_t bal = g.ballot(ok);
           if (bal != 0) {
@@ -1275,11 +1374,11 @@ struct Search {
           double best = 2147483647.0;
           uint32_t code = kNone;
           for (int i = g.lane; i < n; i += Group::W) {
-            if (M.curQ[i] != -1) {
+            if (S.curQ[i] != -1) {
               continue;
             }
             for (int j = i + 1; j < n; ++j) {
-              if (M.curQ[j] != -1) {
+              if (S.curQ[j] != -1) {
                 continue;
               }
               const double d = dRev(i, j);
@@ -1318,7 +1417,8 @@ struct Search {
   struct LayerStats {
     uint64_t expanded = 0, expAfterFirst = 0, expAfterOpt = 0, solNodes = 0,
              solAfterOpt = 0;
-    uint32_t result = kNone;
+    uint32_t result = kNone;  // pool index; kNone with rootResult = the root
+    bool rootResult = false;
     int32_t early = 0;
   };
 
@@ -1334,6 +1434,16 @@ struct Search {
     nCons = ldg(I.circ.consOff + l + 1) - loc;
     cons = I.circ.cons + loc;
     fidK = nCons == 0 ? kNone : nCons - 1;
+    const uint32_t fa = ldg(I.circ.firstAfter + l);
+    const uint32_t avail = I.circ.nTwoQ - fa;
+    nLook = C.lookahead == 0 ? 0U
+                             : (avail < C.nFactors ? avail : C.nFactors);
+    lookLayers = I.circ.twoQ + fa;
+    maskReady = false;
+  }
+
+  // bit mask of getConsideredQubits(layer); built on the first expansion
+  QMG_HD void buildMask() {
     g.sync();
     for (int w = g.lane; w < (n + 31) / 32; w += Group::W) {
       S.consMask[w] = 0;
@@ -1345,6 +1455,7 @@ struct Search {
         S.consMask[q >> 5] |= 1U << (q & 31);
       }
     }
+    maskReady = true;
     g.sync();
   }
 
@@ -1352,18 +1463,12 @@ struct Search {
     nPool = 0;
     nOpen = 0;
     nextId = 0;
+    tableMode = false;
     ++M.stamp;
     // root node from the mapper's current layout
-    for (int i = g.lane; i < n; i += Group::W) {
-      S.Q[i] = M.curQ[i];
-      S.L[i] = M.curL[i];
-    }
+    pQ = S.curQ;
+    pL = S.curL;
     g.sync();
-    uint64_t hsh = 0;
-    for (int i = g.lane; i < n; i += Group::W) {
-      hsh += cellHash(i, S.Q[i]);
-    }
-    hsh = gsum64(g, hsh);
     ParentCosts pc;
     pc.fixed = 0.;
     pc.shared = 0;
@@ -1376,17 +1481,30 @@ struct Search {
     } else if (g.lane == 0) {
       Child out;
       scoreGateCount(0, 0, pc, out, M.nsw);
+      out.a = 0;
+      out.b = 0;
       S.ch[0] = out;
     }
     g.sync();
-    if (g.lane == 0) {
-      S.ch[0].hash = hsh;
-      S.ch[0].a = 0;
-      S.ch[0].b = 0;
-    }
-    g.sync();
     scoreLookahead(1, true);
+    if (S.ch[0].valid != 0 && C.tight != 0) {
+      // the root is a goal and the heuristic is tight: the first pop ends
+      // the search (:585-599) - no node record is needed
+      nextId = 1;
+      st.solNodes = 1;
+      st.rootResult = true;
+      return ST_OK;
+    }
     {
+      uint64_t hsh = 0;
+      for (int i = g.lane; i < n; i += Group::W) {
+        hsh += cellHash(i, pQ[i]);
+      }
+      hsh = gsum64(g, hsh);
+      if (g.lane == 0) {
+        S.ch[0].hash = hsh;
+      }
+      g.sync();
       const Child root = S.ch[0];
       if (!push(root, kNone, 0, true)) {
         return ST_POOL;
@@ -1478,48 +1596,58 @@ struct Search {
     }
     LayerStats st;
     const int rc = astar(st);
-    if (g.lane == 0) {
-      I.counters[0] += st.expanded;
-      I.counters[1] += nextId;
-    }
+    totExpanded += st.expanded;
+    totGenerated += nextId;
     if (rc != ST_OK) {
       return rc;
     }
-    const uint32_t res = st.result;
-    const NodeHdr* h = hdr(res);
-    const int16_t* rq = nodeQ(res);
-    const int16_t* rl = nodeL(res);
     g.sync();
-    for (int i = g.lane; i < n; i += Group::W) {
-      M.curQ[i] = rq[i];
-      M.curL[i] = rl[i];
-      if (finalPass && I.layerQ != nullptr) {
-        I.layerQ[static_cast<size_t>(l) * n + i] = rq[i];
+    // the 15 eight-byte fields of LayerOut are staged in shared memory and
+    // written by 15 lanes as one coalesced 120-byte store
+    uint64_t* stage = reinterpret_cast<uint64_t*>(S.lookPen);
+    uint32_t d = 0;
+    if (st.rootResult) {
+      if (finalPass && g.lane == 0) {
+        const Child& r = S.ch[0];
+        LayerOut o{};
+        o.cost_fixed = r.fixed;
+        o.cost_fixed_reversals = r.rev;
+        o.cost_heur = r.heur;
+        o.lookahead_penalty = r.look;
+        o.layoutHash = 0;
+        o.depth = 0;
+        o.resultId = 0;
+        *reinterpret_cast<LayerOut*>(stage) = o;
       }
-    }
-    if (finalPass) {
-      const uint32_t d = h->depth;
-      if (g.lane == 0) {
-        LayerOut& o = I.layers[l];
+      if (finalPass && I.layerQ != nullptr) {
+        for (int i = g.lane; i < n; i += Group::W) {
+          I.layerQ[static_cast<size_t>(l) * n + i] = S.curQ[i];
+        }
+      }
+    } else {
+      const uint32_t res = st.result;
+      const NodeHdr* h = hdr(res);
+      const int16_t* rq = nodeQ(res);
+      const int16_t* rl = nodeL(res);
+      d = h->depth;
+      for (int i = g.lane; i < n; i += Group::W) {
+        const int16_t vq = rq[i];
+        S.curQ[i] = vq;
+        S.curL[i] = rl[i];
+        if (finalPass && I.layerQ != nullptr) {
+          I.layerQ[static_cast<size_t>(l) * n + i] = vq;
+        }
+      }
+      if (finalPass && g.lane == 0) {
+        LayerOut o{};
         o.cost_fixed = h->fixed;
         o.cost_fixed_reversals = h->rev;
         o.cost_heur = h->heur;
         o.lookahead_penalty = h->look;
-        o.expanded = st.expanded;
-        o.generated = nextId;
-        o.expAfterFirst = st.expAfterFirst;
-        o.expAfterOpt = st.expAfterOpt;
-        o.solNodes = st.solNodes;
-        o.solAfterOpt = st.solAfterOpt;
         o.layoutHash = h->hash;
         o.depth = d;
         o.resultId = h->id;
-        o.swapOff = swapTotal;
-        o.nSwaps = d;
-        o.placeOff = placeBefore;
-        o.nPlace = nPlace - placeBefore;
-        o.early = st.early;
-        o.status = ST_OK;
+        *reinterpret_cast<LayerOut*>(stage) = o;
         // swaps root -> result
         if (I.swaps != nullptr && swapTotal + d <= I.swapCap) {
           uint32_t cur = res;
@@ -1530,6 +1658,29 @@ struct Search {
             cur = c->parent;
           }
         }
+      }
+    }
+    if (finalPass) {
+      if (g.lane == 0) {
+        LayerOut& o = *reinterpret_cast<LayerOut*>(stage);
+        o.expanded = st.expanded;
+        o.generated = nextId;
+        o.expAfterFirst = st.expAfterFirst;
+        o.expAfterOpt = st.expAfterOpt;
+        o.solNodes = st.solNodes;
+        o.solAfterOpt = st.solAfterOpt;
+        o.swapOff = swapTotal;
+        o.nSwaps = d;
+        o.placeOff = placeBefore;
+        o.nPlace = nPlace - placeBefore;
+        o.early = st.early;
+        o.status = ST_OK;
+      }
+      g.sync();
+      uint64_t* dst = reinterpret_cast<uint64_t*>(I.layers + l);
+      for (int k = g.lane; k < static_cast<int>(sizeof(LayerOut) / 8);
+           k += Group::W) {
+        dst[k] = stage[k];
       }
       swapTotal += d;
       if (I.swaps != nullptr && swapTotal > I.swapCap) {
@@ -1544,24 +1695,20 @@ struct Search {
   QMG_HD void run() {
     const uint32_t nL = I.circ.nLayers;
     for (int i = g.lane; i < n; i += Group::W) {
-      M.curQ[i] = -1;
-      M.curL[i] = -1;
+      S.curQ[i] = -1;
+      S.curL[i] = -1;
     }
     g.sync();
     if (I.initLoc != nullptr) {
       for (int i = g.lane; i < n; i += Group::W) {
         const int16_t p = I.initLoc[i];
-        M.curL[i] = p;
+        S.curL[i] = p;
         if (p >= 0) {
-          M.curQ[p] = static_cast<int16_t>(i);
+          S.curQ[p] = static_cast<int16_t>(i);
         }
       }
     }
     g.sync();
-    if (g.lane == 0) {
-      I.counters[0] = 0;
-      I.counters[1] = 0;
-    }
     uint32_t swapTotal = 0;
     int rc = ST_OK;
     uint32_t doneLayers = 0;
@@ -1576,7 +1723,7 @@ struct Search {
     if (rc == ST_OK) {
       if (I.startL != nullptr) {
         for (int i = g.lane; i < n; i += Group::W) {
-          I.startL[i] = M.curL[i];
+          I.startL[i] = S.curL[i];
         }
       }
       const uint32_t first = I.firstLayer;
@@ -1593,14 +1740,16 @@ struct Search {
     }
     g.sync();
     for (int i = g.lane; i < n; i += Group::W) {
-      I.finalQ[i] = M.curQ[i];
-      I.finalL[i] = M.curL[i];
+      I.finalQ[i] = S.curQ[i];
+      I.finalL[i] = S.curL[i];
     }
     if (g.lane == 0) {
       I.summary[0] = swapTotal;
       I.summary[1] = nPlace;
       I.summary[2] = doneLayers;
       I.summary[3] = static_cast<uint32_t>(rc);
+      I.counters[0] = totExpanded;
+      I.counters[1] = totGenerated;
     }
     g.sync();
   }

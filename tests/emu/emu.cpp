@@ -79,7 +79,10 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     return fail(QMG_BAD_ARG, msg);
   }
   const ArchView A = arch->view();
-  const CfgView C = toCfgView(*cfg);
+  CfgView C = toCfgView(*cfg);
+  const std::vector<double> factors = lookaheadFactors(*cfg, 1U << 20);
+  C.factors = factors.data();
+  C.nFactors = static_cast<uint32_t>(factors.size());
   const int n = A.n;
   if (poolNodes == 0) {
     poolNodes = 1U << 16;
@@ -93,12 +96,10 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
   std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8);
   std::vector<OpenEntry> open(poolNodes);
   std::vector<uint64_t> table(tableSize, 0);
-  std::vector<int16_t> cur(2 * static_cast<size_t>(n));
-  std::vector<int16_t> ql(2 * static_cast<size_t>(n));
+  std::vector<int16_t> ql(4 * static_cast<size_t>(n));
   std::vector<uint32_t> consMask((n + 31) / 32 + 1);
   std::vector<Child> ch(kChunk);
   std::vector<double> lookPen(kChunk / 2 * kLookBlock);
-  std::vector<uint32_t> lookLayers(kLookBlock + 2);
   uint32_t stamp = 0;
   for (size_t ii = 0; ii < nInstances; ++ii) {
     const qmg_instance& in = instances[ii];
@@ -114,8 +115,6 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.pool = reinterpret_cast<uint8_t*>(poolStore.data());
     M.open = open.data();
     M.table = table.data();
-    M.curQ = cur.data();
-    M.curL = cur.data() + n;
     M.nsw = nsw.data();
     M.poolCap = poolNodes;
     M.recBytes = recBytes;
@@ -125,10 +124,11 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     Scratch S{};
     S.Q = ql.data();
     S.L = ql.data() + n;
+    S.curQ = ql.data() + 2 * n;
+    S.curL = ql.data() + 3 * n;
     S.consMask = consMask.data();
     S.ch = ch.data();
     S.lookPen = lookPen.data();
-    S.lookLayers = lookLayers.data();
     InstView I{};
     I.circ = fc.view();
     I.initLoc = in.initial_locations;
