@@ -826,9 +826,15 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     M.maxG = maxG;
   }
   b->mem.upload(hMem, s);
-  CU(cudaFuncSetAttribute(route_kernel,
-                          cudaFuncAttributeMaxDynamicSharedMemorySize,
-                          static_cast<int>(b->smemBytes)));
+  {
+    const int sb = static_cast<int>(b->smemBytes);
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    CU(cudaFuncSetAttribute(route_kernel<0>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<1>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<2>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<3>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<4>, attr, sb));
+  }
   b->h2dMs = tm.stop();
   *out = b.release();
   return QMG_OK;
@@ -843,9 +849,30 @@ int batchRun(qmg_batch* b, qmg_route_stats* stats) {
   EventTimer tm(s);
   tm.start();
   if (b->nInst > 0) {
-    route_kernel<<<b->grid, kWarpsPerCta * 32, b->smemBytes, s>>>(
-        b->arch->view(), b->cfg, b->inst.p, b->order.p,
-        static_cast<uint32_t>(b->nInst), b->mem.p, b->ticket.p, b->sl);
+    const ArchView av = b->arch->view();
+    const uint32_t nI = static_cast<uint32_t>(b->nInst);
+    const dim3 blk(kWarpsPerCta * 32);
+#define QMG_LAUNCH(HH)                                                         \
+  route_kernel<HH><<<b->grid, blk, b->smemBytes, s>>>(                         \
+      av, b->cfg, b->inst.p, b->order.p, nI, b->mem.p, b->ticket.p, b->sl)
+    switch (b->cfg.heuristic) {
+    case 0:
+      QMG_LAUNCH(0);
+      break;
+    case 1:
+      QMG_LAUNCH(1);
+      break;
+    case 2:
+      QMG_LAUNCH(2);
+      break;
+    case 3:
+      QMG_LAUNCH(3);
+      break;
+    default:
+      QMG_LAUNCH(4);
+      break;
+    }
+#undef QMG_LAUNCH
     CU(cudaGetLastError());
     ++b->launches;
   }

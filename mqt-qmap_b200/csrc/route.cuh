@@ -14,6 +14,9 @@
 namespace qmg {
 
 constexpr int kWarpsPerCta = 4;
+#ifndef QMG_MIN_CTAS
+#define QMG_MIN_CTAS 8
+#endif
 
 struct SmemLayout {
   uint32_t bytesPerWarp;
@@ -41,7 +44,8 @@ inline SmemLayout smemLayout(int n) {
   return s;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+template <int H>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
     route_kernel(ArchView A, CfgView C, const InstView* __restrict__ inst,
                  const uint32_t* __restrict__ order, uint32_t nInst,
                  SearchMem* __restrict__ mem, uint32_t* __restrict__ ticket,
@@ -70,7 +74,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
       break;
     }
     const InstView I = inst[order[t]];
-    Search s(A, C, I, M, S);
+    Search<H> s(A, C, I, M, S);
     s.run();
     __syncwarp();
   }

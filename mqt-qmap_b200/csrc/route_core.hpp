@@ -23,9 +23,11 @@
 #if defined(__CUDACC__)
 #define QMG_HD __host__ __device__ __forceinline__
 #define QMG_D __device__ __forceinline__
+#define QMG_NOUNROLL _Pragma("unroll 1")
 #else
 #define QMG_HD inline
 #define QMG_D inline
+#define QMG_NOUNROLL
 #endif
 
 namespace qmg {
@@ -316,7 +318,12 @@ QMG_HD void gargmin(const Group& g, double& v, uint32_t& i) {
 // ---------------------------------------------------------------------------
 // the search of one instance
 // ---------------------------------------------------------------------------
-struct Search {
+// H = qmg_heuristic (0..4): one kernel instantiation per heuristic keeps the
+// resident code of a launch small (the instruction cache, not the data path,
+// bounds this kernel)
+template <int H> struct Search {
+  static constexpr bool kFid = (H == 4);
+  static constexpr bool kTight = !kFid;  // isTight, Heuristic.hpp:96-110
   const ArchView& A;
   const CfgView& C;
   const InstView& I;
@@ -411,6 +418,7 @@ struct Search {
     }
     int p1 = q1;
     int p2 = q2;
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
       if (e.q1 == q1) {
@@ -428,7 +436,7 @@ struct Search {
       const int physQ3 = pL[p1];
       const int physQ4 = pL[p2];
       double e1b, e1n, e2b, e2n;
-      if (C.fidelityAware) {
+      if (kFid) {
         e1b = fmin(fidDist(a, physQ3, 0), fidDist(physQ3, a, 0));
         e1n = fmin(fidDist(b, physQ3, 0), fidDist(physQ3, b, 0));
         e2b = fmin(fidDist(b, physQ4, 0), fidDist(physQ4, b, 0));
@@ -451,9 +459,11 @@ struct Search {
   QMG_HD double sharedSwapReduction(uint16_t* nsw, uint32_t cnt,
                                     uint32_t shared) const {
     // std::sort(..., greater): insertion sort on small per-lane arrays
+    QMG_NOUNROLL
     for (uint32_t i = 1; i < cnt; ++i) {
       const uint16_t v = nsw[i];
       uint32_t j = i;
+      QMG_NOUNROLL
       while (j > 0 && nsw[j - 1] < v) {
         nsw[j] = nsw[j - 1];
         --j;
@@ -461,8 +471,10 @@ struct Search {
       nsw[j] = v;
     }
     uint64_t maxShared = 0;
+    QMG_NOUNROLL
     for (uint32_t i = 0; i + 1 < cnt; ++i) {
       uint32_t edgeShared = 0;
+      QMG_NOUNROLL
       for (uint32_t j = i + 1; j < cnt && edgeShared < nsw[i]; ++j) {
         if (nsw[j] > 0) {
           ++edgeShared;
@@ -488,7 +500,7 @@ struct Search {
     const int q2 = root ? -2 : pQ[b];
     out.a = static_cast<uint16_t>(a);
     out.b = static_cast<uint16_t>(b);
-    const int h = C.heuristic;
+    constexpr int h = H;
     // Node::sharedSwaps is only read by heuristics 2 and 3 (:1237-1241)
     out.shared = pc.shared;
     if (!root && (h == 2 || h == 3)) {
@@ -506,6 +518,7 @@ struct Search {
     double hShared = 0.;
     double costReversals = 0.;
     uint32_t cnt = 0;
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
       const int p1 = locAfter(e.q1, q1, q2, a, b);
@@ -606,6 +619,7 @@ struct Search {
     const uint32_t hi = ldg(I.circ.g2Off + ll + 1);
     const bool isMax = (C.lookahead == 1);
     double penalty = 0.;
+    QMG_NOUNROLL
     for (uint32_t i = lo; i < hi; ++i) {
       const Gate2 e = ldGate(I.circ.g2 + i);
       const int loc1 = locAfter(e.q1, q1, q2, a, b);
@@ -619,6 +633,7 @@ struct Search {
         const bool firstFree = loc1 < 0;
         const int loc = firstFree ? loc2 : loc1;
         double mn = DBL_MAX;
+        QMG_NOUNROLL
         for (int j = 0; j < n; ++j) {
           const int qj = (j == a) ? q2 : ((j == b) ? q1 : pQ[j]);
           if (qj != -1) {
@@ -658,6 +673,7 @@ struct Search {
   // operation order (acc += factor_i * penalty_i).
   QMG_HD void scoreLookahead(int cnt, bool rootOnly) {
     if (C.lookahead == 0 || nLook == 0) {
+      QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
         S.ch[c].look = 0.;
       }
@@ -665,17 +681,21 @@ struct Search {
       return;
     }
     constexpr int kHalf = kChunk / 2;
+    QMG_NOUNROLL
     for (int c0 = 0; c0 < cnt; c0 += kHalf) {
       const int nc = (cnt - c0) < kHalf ? (cnt - c0) : kHalf;
+      QMG_NOUNROLL
       for (int c = g.lane; c < nc; c += Group::W) {
         S.ch[c0 + c].look = 0.;
       }
+      QMG_NOUNROLL
       for (uint32_t s0 = 0; s0 < nLook; s0 += kLookBlock) {
         const uint32_t nb =
             (nLook - s0) < static_cast<uint32_t>(kLookBlock)
                 ? (nLook - s0)
                 : static_cast<uint32_t>(kLookBlock);
         g.sync();
+        QMG_NOUNROLL
         for (int it = g.lane; it < nc * kLookBlock; it += Group::W) {
           const int c = it / kLookBlock;
           const uint32_t sl = static_cast<uint32_t>(it % kLookBlock);
@@ -694,8 +714,10 @@ struct Search {
               lookaheadPenalty(ldg(lookLayers + s0 + sl), a, b, q1, q2);
         }
         g.sync();
+        QMG_NOUNROLL
         for (int c = g.lane; c < nc; c += Group::W) {
           double acc = S.ch[c0 + c].look;
+          QMG_NOUNROLL
           for (uint32_t sl = 0; sl < nb; ++sl) {
             acc += ldg(C.factors + s0 + sl) * S.lookPen[c * kLookBlock + sl];
           }
@@ -723,12 +745,14 @@ struct Search {
     }
     double fixed = root ? 0. : pc.fixed;
     if (root) {
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
         fixed += e.mult * ldg(A.c1 + pL[e.q]);
       }
     }
     uint32_t nValid = 0;
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
       const int p3 = locAfter(e.q1, q1, q2, a, b);
@@ -762,6 +786,7 @@ struct Search {
       // :934-952
       int m1 = 0;
       int m2 = 0;
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
         if (e.q == q1) {
@@ -778,11 +803,13 @@ struct Search {
     // heuristicFidelityBestLocation
     double costHeur = 0.;
     double savings = 0.;
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G1; ++i) {
       const Gate1 e = ldGate1(gates1 + i);
       const int loc = locAfter(e.q, q1, q2, a, b);
       const double curr = ldg(A.c1 + loc);
       double best = 0.;
+      QMG_NOUNROLL
       for (int p = g.lane; p < n; p += Group::W) {
         const double cp = ldg(A.c1 + p);
         if (cp >= curr) {
@@ -794,11 +821,13 @@ struct Search {
       best = gmax(g, best);
       savings += best;
     }
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
       const int l1 = locAfter(e.q1, q1, q2, a, b);
       const int l2 = locAfter(e.q2, q1, q2, a, b);
       double sc = DBL_MAX;
+      QMG_NOUNROLL
       for (int k = g.lane; k < A.nE; k += Group::W) {
         const int q3 = ldg(A.edges + 2 * k);
         const int q4 = ldg(A.edges + 2 * k + 1);
@@ -876,6 +905,7 @@ struct Search {
     }
     const int16_t* qx = nodeQ(x.idx);
     const int16_t* qy = nodeQ(y.idx);
+    QMG_NOUNROLL
     for (int i = 0; i < n; i += 4) {
       const uint64_t kx = lexChunk(qx, i);
       const uint64_t ky = lexChunk(qy, i);
@@ -915,6 +945,7 @@ struct Search {
     best.idx = kNone;
     best.nValid = 0;
     best.valid = 0;
+    QMG_NOUNROLL
     for (uint32_t i = g.lane; i < nOpen; i += Group::W) {
       const OpenEntry e = M.open[i];
       if (bestPos == kNone || hasPriority(e, best)) {
@@ -940,6 +971,7 @@ struct Search {
       cand = cand && (best.nValid + 1U == nv);
       m = g.ballot(cand);
       const int16_t* q = cand ? nodeQ(best.idx) : nullptr;
+      QMG_NOUNROLL
       for (int i = 0; i < n && popc32(m) > 1; i += 4) {
         const uint64_t k = cand ? lexChunk(q, i) : 0ULL;
         const uint64_t kmx = gmaxU64(k);
@@ -977,6 +1009,7 @@ struct Search {
     const int b = ch.b;
     const int q1 = root ? -2 : pQ[a];
     const int q2 = root ? -2 : pQ[b];
+    QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       int16_t vq = pQ[i];
       int16_t vl = pL[i];
@@ -1032,6 +1065,7 @@ struct Search {
     const int a = ch.a;
     const int b = ch.b;
     bool diff = false;
+    QMG_NOUNROLL
     for (int i0 = 0; i0 < n; i0 += Group::W) {
       const int i = i0 + g.lane;
       if (i < n) {
@@ -1056,10 +1090,12 @@ struct Search {
   QMG_HD void buildTable() {
     g.sync();
     if (g.lane == 0) {
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < nOpen; ++i) {
         const OpenEntry e = M.open[i];
         uint32_t slot = static_cast<uint32_t>(e.hash ^ (e.hash >> 32)) &
                         M.tableMask;
+        QMG_NOUNROLL
         while (static_cast<uint32_t>(M.table[slot] >> 32) == M.stamp) {
           slot = (slot + 1) & M.tableMask;
         }
@@ -1084,9 +1120,11 @@ struct Search {
       buildTable();
     }
     if (!tableMode) {
+      QMG_NOUNROLL
       for (uint32_t i0 = 0; i0 < nOpen && found == kNone; i0 += Group::W) {
         const uint32_t i = i0 + g.lane;
         uint32_t m = g.ballot(i < nOpen && M.open[i].hash == h);
+        QMG_NOUNROLL
         while (m != 0 && found == kNone) {
           const int src = ctz32(m);
           m &= m - 1;
@@ -1147,14 +1185,16 @@ struct Search {
     return true;
   }
 
-  // score the cnt children in S.ch (their a/b are set) and push them in order
-  QMG_HD bool flushChildren(int cnt, uint32_t parentIdx, const ParentCosts& pc,
-                            uint64_t parentHash, uint32_t depth) {
+  // score the cnt nodes in S.ch (their a/b are set; root: the layout itself):
+  // costs, layout hash and lookahead penalty
+  QMG_HD void evaluate(int cnt, bool root, const ParentCosts& pc,
+                       uint64_t parentHash) {
     g.sync();
-    if (C.fidelityAware) {
+    if (kFid) {
+      QMG_NOUNROLL
       for (int c = 0; c < cnt; ++c) {
         Child out;
-        scoreFidelity(S.ch[c].a, S.ch[c].b, pc, out);
+        scoreFidelity(root ? 0 : S.ch[c].a, root ? 0 : S.ch[c].b, pc, out);
         if (g.lane == 0) {
           S.ch[c].fixed = out.fixed;
           S.ch[c].rev = out.rev;
@@ -1165,9 +1205,12 @@ struct Search {
         }
       }
     } else {
+      QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
         Child out;
-        scoreGateCount(S.ch[c].a, S.ch[c].b, pc, out,
+        const int a = root ? 0 : S.ch[c].a;
+        const int b = root ? 0 : S.ch[c].b;
+        scoreGateCount(a, b, pc, out,
                        M.nsw + static_cast<size_t>(g.lane) * M.maxG);
         S.ch[c].fixed = out.fixed;
         S.ch[c].rev = out.rev;
@@ -1175,63 +1218,50 @@ struct Search {
         S.ch[c].shared = out.shared;
         S.ch[c].nValid = out.nValid;
         S.ch[c].valid = out.valid;
+        if (!root) {
+          const int q1 = pQ[a];
+          const int q2 = pQ[b];
+          S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
+                         cellHash(a, q2) + cellHash(b, q1);
+        }
       }
     }
-    for (int c = g.lane; c < cnt; c += Group::W) {
-      const int a = S.ch[c].a;
-      const int b = S.ch[c].b;
-      const int q1 = pQ[a];
-      const int q2 = pQ[b];
-      S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
-                     cellHash(a, q2) + cellHash(b, q1);
+    if (kFid && !root) {
+      QMG_NOUNROLL
+      for (int c = g.lane; c < cnt; c += Group::W) {
+        const int a = S.ch[c].a;
+        const int b = S.ch[c].b;
+        const int q1 = pQ[a];
+        const int q2 = pQ[b];
+        S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
+                       cellHash(a, q2) + cellHash(b, q1);
+      }
     }
     g.sync();
-    scoreLookahead(cnt, false);
-    for (int c = 0; c < cnt; ++c) {
-      const Child ch = S.ch[c];
-      if (!push(ch, parentIdx, depth, false)) {
-        return false;
-      }
-    }
-    return true;
+    scoreLookahead(cnt, root);
   }
 
-  // expandNode :698-727.  The candidate order (considered qubit ascending,
-  // then coupling edge ascending) and the usedSwaps rule are reproduced by a
-  // closed form: a swap between two occupied physical qubits is generated
-  // only from the smallest considered qubit of the pair and only on the
-  // smaller of the (up to two) directed edges between them.
-  QMG_HD bool expand(uint32_t parentIdx) {
-    if (!maskReady) {
-      buildMask();
-    }
-    // stage the parent
-    pQ = S.Q;
-    pL = S.L;
-    const int16_t* pq = nodeQ(parentIdx);
-    const int16_t* pl = nodeL(parentIdx);
-    for (int i = g.lane; i < n; i += Group::W) {
-      pQ[i] = pq[i];
-      pL[i] = pl[i];
-    }
-    const NodeHdr* ph = hdr(parentIdx);
-    ParentCosts pc;
-    pc.fixed = ph->fixed;
-    pc.shared = ph->shared;
-    const uint64_t parentHash = ph->hash;
-    const uint32_t depth = ph->depth + 1;
-    g.sync();
+  // expandNode :698-727, resumable.  The candidate order (considered qubit
+  // ascending, then coupling edge ascending) and the usedSwaps rule are
+  // reproduced by a closed form: a swap between two occupied physical qubits
+  // is generated only from the smallest considered qubit of the pair and only
+  // on the smaller of the (up to two) directed edges between them.  Fills
+  // S.ch[0..cnt) with up to kChunk swaps and sets enumDone when the parent is
+  // exhausted.
+  uint32_t enumCi = 0, enumK = 0;
+  bool enumDone = true;
+
+  QMG_HD int gatherChunk() {
     int cnt = 0;
-    for (uint32_t ci = 0; ci < nCons; ++ci) {
-      const int q = ldg(cons + ci);
+    QMG_NOUNROLL
+    while (enumCi < nCons) {
+      const int q = ldg(cons + enumCi);
       const int p = pL[q];
-      if (p < 0) {
-        continue;
-      }
-      const uint32_t lo = ldg(A.incOff + p);
-      const uint32_t hi = ldg(A.incOff + p + 1);
-      for (uint32_t k0 = lo; k0 < hi; k0 += Group::W) {
-        const uint32_t k = k0 + g.lane;
+      const uint32_t lo = p < 0 ? 0U : ldg(A.incOff + p);
+      const uint32_t hi = p < 0 ? 0U : ldg(A.incOff + p + 1);
+      QMG_NOUNROLL
+      while (lo + enumK < hi) {
+        const uint32_t k = lo + enumK + g.lane;
         bool keep = false;
         int ea = 0;
         int eb = 0;
@@ -1253,31 +1283,24 @@ struct Search {
         }
         const uint32_t bal = g.ballot(keep);
         const int add = popc32(bal);
-        if (add == 0) {
-          continue;
-        }
         if (cnt + add > kChunk) {
-          if (!flushChildren(cnt, parentIdx, pc, parentHash, depth)) {
-            return false;
-          }
-          cnt = 0;
+          return cnt;  // resume with this block in the next chunk
         }
         if (keep) {
-          const int rank =
-              popc32(bal & ((1U << g.lane) - 1U));
+          const int rank = popc32(bal & ((1U << g.lane) - 1U));
           S.ch[cnt + rank].a = static_cast<uint16_t>(ea);
           S.ch[cnt + rank].b = static_cast<uint16_t>(eb);
         }
         cnt += add;
+        enumK += Group::W;
       }
+      ++enumCi;
+      enumK = 0;
     }
-    if (cnt > 0) {
-      if (!flushChildren(cnt, parentIdx, pc, parentHash, depth)) {
-        return false;
-      }
-    }
-    return true;
+    enumDone = true;
+    return cnt;
   }
+
 
   // ------------------------------------------------------------------------
   // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on S.curQ / S.curL
@@ -1301,6 +1324,7 @@ struct Search {
   }
 
   QMG_HD int firstFree() const {
+    QMG_NOUNROLL
     for (int p0 = 0; p0 < n; p0 += Group::W) {
       const int p = p0 + g.lane;
       const uint32_t bal = g.ballot(p < n && S.curQ[p] == -1);
@@ -1315,6 +1339,7 @@ struct Search {
     const int src = S.curL[source];
     double best = DBL_MAX;
     uint32_t pos = kNone;
+    QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       if (S.curQ[i] == -1) {
         const double d = dRev(src, i);
@@ -1334,7 +1359,8 @@ struct Search {
 
   QMG_HD bool mapUnmappedGates() {
     g.sync();
-    if (C.fidelityAware) {
+    if (kFid) {
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
         if (S.curL[e.q] == -1) {
@@ -1345,6 +1371,7 @@ struct Search {
         }
       }
     }
+    QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
       const int l1 = S.curL[e.q1];
@@ -1353,6 +1380,7 @@ struct Search {
         // first coupling edge (ascending) with both ends free
         int ca = -1;
         int cb = -1;
+        QMG_NOUNROLL
         for (int k0 = 0; k0 < A.nE; k0 += Group::W) {
           const int k = k0 + g.lane;
           bool ok = false;
@@ -1373,10 +1401,12 @@ struct Search {
           // (i, j) order
           double best = 2147483647.0;
           uint32_t code = kNone;
+          QMG_NOUNROLL
           for (int i = g.lane; i < n; i += Group::W) {
             if (S.curQ[i] != -1) {
               continue;
             }
+            QMG_NOUNROLL
             for (int j = i + 1; j < n; ++j) {
               if (S.curQ[j] != -1) {
                 continue;
@@ -1445,11 +1475,13 @@ struct Search {
   // bit mask of getConsideredQubits(layer); built on the first expansion
   QMG_HD void buildMask() {
     g.sync();
+    QMG_NOUNROLL
     for (int w = g.lane; w < (n + 31) / 32; w += Group::W) {
       S.consMask[w] = 0;
     }
     g.sync();
     if (g.lane == 0) {
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < nCons; ++i) {
         const int q = ldg(cons + i);
         S.consMask[q >> 5] |= 1U << (q & 31);
@@ -1465,56 +1497,98 @@ struct Search {
     nextId = 0;
     tableMode = false;
     ++M.stamp;
-    // root node from the mapper's current layout
-    pQ = S.curQ;
-    pL = S.curL;
-    g.sync();
+    const bool splittable =
+        C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
+    // one loop iteration = evaluate one chunk of nodes (first the root from
+    // the mapper's current layout, then the children of the node being
+    // expanded) and push them; when a parent is exhausted the next node is
+    // taken from the open list.  Scoring, push and selection have a single
+    // call site each, which keeps the kernel's resident code small.
+    bool rootMode = true;
+    bool found = false;
+    double bestFixedTotal = 0.;
+    uint32_t parent = kNone;
+    uint32_t depth = 0;
+    uint64_t parentHash = 0;
     ParentCosts pc;
     pc.fixed = 0.;
     pc.shared = 0;
-    if (C.fidelityAware) {
-      Child out;
-      scoreFidelity(0, 0, pc, out);
-      if (g.lane == 0) {
-        S.ch[0] = out;
-      }
-    } else if (g.lane == 0) {
-      Child out;
-      scoreGateCount(0, 0, pc, out, M.nsw);
-      out.a = 0;
-      out.b = 0;
-      S.ch[0] = out;
-    }
-    g.sync();
-    scoreLookahead(1, true);
-    if (S.ch[0].valid != 0 && C.tight != 0) {
-      // the root is a goal and the heuristic is tight: the first pop ends
-      // the search (:585-599) - no node record is needed
-      nextId = 1;
-      st.solNodes = 1;
-      st.rootResult = true;
-      return ST_OK;
-    }
-    {
-      uint64_t hsh = 0;
-      for (int i = g.lane; i < n; i += Group::W) {
-        hsh += cellHash(i, pQ[i]);
-      }
-      hsh = gsum64(g, hsh);
-      if (g.lane == 0) {
-        S.ch[0].hash = hsh;
-      }
-      g.sync();
-      const Child root = S.ch[0];
-      if (!push(root, kNone, 0, true)) {
-        return ST_POOL;
-      }
-    }
-    const bool splittable =
-        C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
-    bool found = false;
-    double bestFixedTotal = 0.;
+    pQ = S.curQ;
+    pL = S.curL;
+    enumDone = true;
+    QMG_NOUNROLL
     for (;;) {
+      const int cnt = rootMode ? 1 : gatherChunk();
+      if (cnt > 0) {
+        evaluate(cnt, rootMode, pc, parentHash);
+        if (rootMode) {
+          if (S.ch[0].valid != 0 && kTight) {
+            // the root is a goal and the heuristic is tight: the first pop
+            // ends the search (:585-599) - no node record is needed
+            nextId = 1;
+            st.solNodes = 1;
+            st.rootResult = true;
+            return ST_OK;
+          }
+          uint64_t hsh = 0;
+          QMG_NOUNROLL
+          for (int i = g.lane; i < n; i += Group::W) {
+            hsh += cellHash(i, pQ[i]);
+          }
+          hsh = gsum64(g, hsh);
+          if (g.lane == 0) {
+            S.ch[0].hash = hsh;
+            S.ch[0].a = 0;
+            S.ch[0].b = 0;
+          }
+          g.sync();
+        }
+        QMG_NOUNROLL
+        for (int c = 0; c < cnt; ++c) {
+          const Child ch = S.ch[c];
+          if (!push(ch, parent, depth, rootMode)) {
+            return ST_POOL;
+          }
+        }
+      }
+      if (!rootMode) {
+        if (!enumDone) {
+          continue;  // more children of this parent
+        }
+        ++st.expanded;
+        if (found) {
+          ++st.expAfterFirst;
+          ++st.expAfterOpt;
+          if (C.earlyTermination != 0) {
+            uint64_t v = 0;
+            switch (C.earlyTermination) {
+            case 1:
+              v = st.expanded;
+              break;
+            case 2:
+              v = st.expAfterFirst;
+              break;
+            case 3:
+              v = st.expAfterOpt;
+              break;
+            case 4:
+              v = st.solNodes;
+              break;
+            case 5:
+              v = st.solAfterOpt;
+              break;
+            default:
+              break;
+            }
+            if (v >= C.earlyLimit) {
+              st.early = 1;
+              break;
+            }
+          }
+        }
+      }
+      rootMode = false;
+      // ---- next node (:560-602)
       if (nOpen == 0) {
         break;
       }
@@ -1527,9 +1601,9 @@ struct Search {
         return ST_SPLIT;
       }
       const uint32_t cur = top.idx;
+      const NodeHdr* h = hdr(cur);
       if (top.valid) {
         ++st.solNodes;
-        const NodeHdr* h = hdr(cur);
         const double fixedTotal = h->fixed + h->rev + h->look;
         if (!found || fixedTotal < bestFixedTotal) {
           st.result = cur;
@@ -1540,51 +1614,40 @@ struct Search {
           ++st.solAfterOpt;
         }
         found = true;
-        if (C.tight) {
+        if (kTight) {
           break;
         }
       }
       removeOpen(pos);
-      if (!expand(cur)) {
-        return ST_POOL;
+      // ---- stage the node to expand
+      if (!maskReady) {
+        buildMask();
       }
-      ++st.expanded;
-      if (found) {
-        ++st.expAfterFirst;
-        ++st.expAfterOpt;
-        if (C.earlyTermination != 0) {
-          uint64_t v = 0;
-          switch (C.earlyTermination) {
-          case 1:
-            v = st.expanded;
-            break;
-          case 2:
-            v = st.expAfterFirst;
-            break;
-          case 3:
-            v = st.expAfterOpt;
-            break;
-          case 4:
-            v = st.solNodes;
-            break;
-          case 5:
-            v = st.solAfterOpt;
-            break;
-          default:
-            break;
-          }
-          if (v >= C.earlyLimit) {
-            st.early = 1;
-            break;
-          }
-        }
+      pQ = S.Q;
+      pL = S.L;
+      const int16_t* nq = nodeQ(cur);
+      const int16_t* nl = nodeL(cur);
+      QMG_NOUNROLL
+      for (int i = g.lane; i < n; i += Group::W) {
+        pQ[i] = nq[i];
+        pL[i] = nl[i];
       }
+      pc.fixed = h->fixed;
+      pc.shared = h->shared;
+      parentHash = h->hash;
+      depth = h->depth + 1;
+      parent = cur;
+      enumCi = 0;
+      enumK = 0;
+      enumDone = false;
+      g.sync();
     }
     if (!found) {
       return ST_NO_VIABLE;
     }
     return ST_OK;
   }
+
 
   // one aStarMap call incl. mapUnmappedGates; adopts the result layout
   QMG_HD int routeLayer(uint32_t l, bool finalPass, uint32_t& swapTotal) {
@@ -1620,6 +1683,7 @@ struct Search {
         *reinterpret_cast<LayerOut*>(stage) = o;
       }
       if (finalPass && I.layerQ != nullptr) {
+        QMG_NOUNROLL
         for (int i = g.lane; i < n; i += Group::W) {
           I.layerQ[static_cast<size_t>(l) * n + i] = S.curQ[i];
         }
@@ -1630,6 +1694,7 @@ struct Search {
       const int16_t* rq = nodeQ(res);
       const int16_t* rl = nodeL(res);
       d = h->depth;
+      QMG_NOUNROLL
       for (int i = g.lane; i < n; i += Group::W) {
         const int16_t vq = rq[i];
         S.curQ[i] = vq;
@@ -1651,6 +1716,7 @@ struct Search {
         // swaps root -> result
         if (I.swaps != nullptr && swapTotal + d <= I.swapCap) {
           uint32_t cur = res;
+          QMG_NOUNROLL
           for (uint32_t k = d; k > 0; --k) {
             const NodeHdr* c = hdr(cur);
             I.swaps[2 * (swapTotal + k - 1)] = c->swA;
@@ -1678,6 +1744,7 @@ struct Search {
       }
       g.sync();
       uint64_t* dst = reinterpret_cast<uint64_t*>(I.layers + l);
+      QMG_NOUNROLL
       for (int k = g.lane; k < static_cast<int>(sizeof(LayerOut) / 8);
            k += Group::W) {
         dst[k] = stage[k];
@@ -1694,12 +1761,14 @@ struct Search {
   // HeuristicMapper::map :74-91 for one instance
   QMG_HD void run() {
     const uint32_t nL = I.circ.nLayers;
+    QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       S.curQ[i] = -1;
       S.curL[i] = -1;
     }
     g.sync();
     if (I.initLoc != nullptr) {
+      QMG_NOUNROLL
       for (int i = g.lane; i < n; i += Group::W) {
         const int16_t p = I.initLoc[i];
         S.curL[i] = p;
@@ -1712,16 +1781,20 @@ struct Search {
     uint32_t swapTotal = 0;
     int rc = ST_OK;
     uint32_t doneLayers = 0;
+    QMG_NOUNROLL
     for (uint32_t pass = 0; pass < I.passes && rc == ST_OK; ++pass) {
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
         rc = routeLayer(i, false, swapTotal);
       }
+      QMG_NOUNROLL
       for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
         rc = routeLayer(nL - 1 - i, false, swapTotal);
       }
     }
     if (rc == ST_OK) {
       if (I.startL != nullptr) {
+        QMG_NOUNROLL
         for (int i = g.lane; i < n; i += Group::W) {
           I.startL[i] = S.curL[i];
         }
@@ -1730,6 +1803,7 @@ struct Search {
       const uint32_t last =
           (I.nRoute == 0 || first + I.nRoute > nL) ? nL : first + I.nRoute;
       doneLayers = first;
+      QMG_NOUNROLL
       for (uint32_t l = first; l < last; ++l) {
         rc = routeLayer(l, true, swapTotal);
         if (rc != ST_OK) {
@@ -1739,6 +1813,7 @@ struct Search {
       }
     }
     g.sync();
+    QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       I.finalQ[i] = S.curQ[i];
       I.finalL[i] = S.curL[i];

@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(HERE), "csrc", "libqmap_b200.so")
+LIB_PATH = os.environ.get(
+    "QMAP_B200_LIB", os.path.join(os.path.dirname(HERE), "csrc", "libqmap_b200.so"))
 
 QMG_OK, QMG_NO_VIABLE_MAPPING, QMG_SPLIT_LIMIT_HIT, QMG_BAD_ARG = 0, 1, 2, 3
 QMG_CUDA_ERROR, QMG_OOM, QMG_POOL_EXHAUSTED, QMG_NO_DEVICE = 4, 5, 6, 7

@@ -148,8 +148,13 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     uint64_t counters[2] = {0, 0};
     I.summary = summary;
     I.counters = counters;
-    Search s(A, C, I, M, S);
-    s.run();
+    switch (C.heuristic) {
+    case 0: { Search<0> s(A, C, I, M, S); s.run(); break; }
+    case 1: { Search<1> s(A, C, I, M, S); s.run(); break; }
+    case 2: { Search<2> s(A, C, I, M, S); s.run(); break; }
+    case 3: { Search<3> s(A, C, I, M, S); s.run(); break; }
+    default: { Search<4> s(A, C, I, M, S); s.run(); break; }
+    }
     stamp = M.stamp;
     r.n_swaps_total = summary[0];
     r.n_placements_total = summary[1];
