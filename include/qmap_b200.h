@@ -288,7 +288,7 @@ typedef struct {
  * library fails with QMG_BAD_ARG rather than overrun them.
  */
 typedef struct {
-  qmg_layer_result* layers; /* capacity n_layers of the instance */
+  qmg_layer_result* layers; /* capacity n_layers of the instance, or NULL */
   uint16_t* swaps;          /* pairs (first, second); capacity swap_capacity */
   uint32_t swap_capacity;
   uint32_t n_swaps_total;
@@ -307,6 +307,10 @@ typedef struct {
                              to split and final_* hold the layout before it */
   uint64_t expanded_nodes;  /* all passes, incl. pseudo-routing */
   uint64_t generated_nodes; /* all passes */
+  /* optional compact per-layer output: number of SWAPs inserted before each
+   * layer of the final pass (n_layers entries).  With layers == NULL this is
+   * all a caller needs to emit the routed circuit (routeCircuit :369-384). */
+  uint16_t* layer_n_swaps;
 } qmg_route_result;
 
 typedef struct {

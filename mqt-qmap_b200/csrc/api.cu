@@ -709,7 +709,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   if (b->wantLayerQ) {
     b->oLayerQ.alloc(std::max<uint64_t>(b->totLayers * n, 1));
   }
-  b->oSummary.alloc(4 * std::max<size_t>(nInst, 1));
+  b->oSummary.alloc(8 * std::max<size_t>(nInst, 1));
   b->oCounters.alloc(2 * std::max<size_t>(nInst, 1));
 
   std::vector<InstView> hInst(nInst);
@@ -744,7 +744,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.layerQ = b->wantLayerQ
                    ? b->oLayerQ.p + static_cast<size_t>(b->layerOff[i]) * n
                    : nullptr;
-    I.summary = b->oSummary.p + 4 * i;
+    I.summary = b->oSummary.p + 8 * i;
     I.counters = b->oCounters.p + 2 * i;
   }
   b->inst.upload(hInst, s);
@@ -898,7 +898,7 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
   const size_t n = static_cast<size_t>(b->n);
   EventTimer tm(s);
   tm.start();
-  std::vector<uint32_t> summary(4 * nI);
+  std::vector<uint32_t> summary(8 * nI);
   std::vector<uint64_t> counters(2 * nI);
   uint64_t bytes = 0;
   auto d2h = [&](void* dst, const void* src, size_t nbytes) {
@@ -913,10 +913,10 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
   uint64_t exp = 0, gen = 0;
   for (size_t i = 0; i < nI; ++i) {
     qmg_route_result& r = results[i];
-    r.n_swaps_total = summary[4 * i];
-    r.n_placements_total = summary[4 * i + 1];
-    r.n_layers_done = summary[4 * i + 2];
-    r.status = static_cast<int32_t>(summary[4 * i + 3]);
+    r.n_swaps_total = summary[8 * i];
+    r.n_placements_total = summary[8 * i + 1];
+    r.n_layers_done = summary[8 * i + 2];
+    r.status = static_cast<int32_t>(summary[8 * i + 3]);
     r.expanded_nodes = counters[2 * i];
     r.generated_nodes = counters[2 * i + 1];
     exp += r.expanded_nodes;

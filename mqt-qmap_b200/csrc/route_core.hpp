@@ -129,7 +129,13 @@ struct InstView {
   int16_t* finalL;
   int16_t* startL;
   int16_t* layerQ;
+  uint16_t* layerNSwaps;  // optional compact per-layer SWAP counts
+  // packed SWAP output: at the end of the instance its SWAPs are appended to
+  // swapsPacked at an offset taken from the batch-wide counter
+  uint16_t* swapsPacked;
+  uint32_t* swapCounter;
   // [0]=nSwapsTotal [1]=nPlaceTotal [2]=nLayersDone [3]=status
+  // [4]=offset of the instance's SWAPs in swapsPacked
   uint32_t* summary;
   uint64_t* counters;  // [0]=expanded [1]=generated (all passes)
 };
@@ -1726,7 +1732,15 @@ template <int H> struct Search {
         }
       }
     }
-    if (finalPass) {
+    if (finalPass && I.layerNSwaps != nullptr && g.lane == 0) {
+      I.layerNSwaps[l] = static_cast<uint16_t>(d > 0xffffU ? 0xffffU : d);
+    }
+    if (finalPass && I.layers == nullptr) {
+      swapTotal += d;
+      if (I.swaps != nullptr && swapTotal > I.swapCap) {
+        return ST_BUFFER;
+      }
+    } else if (finalPass) {
       if (g.lane == 0) {
         LayerOut& o = *reinterpret_cast<LayerOut*>(stage);
         o.expanded = st.expanded;
@@ -1818,7 +1832,27 @@ template <int H> struct Search {
       I.finalQ[i] = S.curQ[i];
       I.finalL[i] = S.curL[i];
     }
+    uint32_t packedOff = 0;
+    if (I.swapsPacked != nullptr && I.swaps != nullptr) {
+      const uint32_t ns = swapTotal <= I.swapCap ? swapTotal : 0U;
+      if (g.lane == 0 && ns > 0) {
+#if defined(__CUDA_ARCH__)
+        packedOff = atomicAdd(I.swapCounter, ns);
+#else
+        packedOff = *I.swapCounter;
+        *I.swapCounter += ns;
+#endif
+      }
+      packedOff = g.bcast(packedOff, 0);
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(I.swaps);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(I.swapsPacked) + packedOff;
+      QMG_NOUNROLL
+      for (uint32_t k = g.lane; k < ns; k += Group::W) {
+        dst[k] = src[k];
+      }
+    }
     if (g.lane == 0) {
+      I.summary[4] = packedOff;
       I.summary[0] = swapTotal;
       I.summary[1] = nPlace;
       I.summary[2] = doneLayers;

@@ -84,6 +84,7 @@ class QmgRouteResult(C.Structure):
         ("start_locations", C.c_void_p), ("layer_qubits", C.c_void_p),
         ("n_layers_done", C.c_uint32), ("status", C.c_int32),
         ("expanded_nodes", C.c_uint64), ("generated_nodes", C.c_uint64),
+        ("layer_n_swaps", C.c_void_p),
     ]
 
 

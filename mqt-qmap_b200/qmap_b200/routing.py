@@ -143,10 +143,16 @@ class RouteOutput:
     final_locations: np.ndarray
     start_locations: np.ndarray
     layer_qubits: np.ndarray | None = None
+    layer_n_swaps: np.ndarray | None = None  # uint16 per layer
+    _offsets: np.ndarray | None = None
 
     def layer_swaps(self, layer: int) -> np.ndarray:
-        r = self.layers[layer]
-        return self.swaps[r["swap_offset"]: r["swap_offset"] + r["n_swaps"]]
+        if self.layers is not None:
+            r = self.layers[layer]
+            return self.swaps[r["swap_offset"]: r["swap_offset"] + r["n_swaps"]]
+        if self._offsets is None:
+            self._offsets = np.concatenate(([0], np.cumsum(self.layer_n_swaps, dtype=np.int64)))
+        return self.swaps[self._offsets[layer]: self._offsets[layer + 1]]
 
 
 @dataclass
@@ -163,10 +169,13 @@ class BatchBuffers:
     fl: np.ndarray = None
     sl: np.ndarray = None
     lq: list = field(default_factory=list)
+    lns: list = field(default_factory=list)
     keep: list = field(default_factory=list)
 
 
-def pack(n: int, items, want_layer_qubits=False, swap_capacity=None) -> BatchBuffers:
+def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False) -> BatchBuffers:
+    """lean: no per-layer qmg_layer_result records, only the compact per-layer
+    SWAP counts (what circuit emission needs)."""
     nI = len(items)
     b = BatchBuffers(n=n, items=list(items))
     b.inst = (QmgInstance * nI)()
@@ -188,14 +197,19 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None) -> BatchBuf
         ins.first_layer = it.first_layer
         ins.n_route_layers = it.n_route_layers
         cap = swap_capacity if swap_capacity is not None else 4 * nl + 256
-        lr = np.zeros(max(nl, 1), dtype=LAYER_RESULT_DTYPE)
+        lr = None if lean else np.zeros(max(nl, 1), dtype=LAYER_RESULT_DTYPE)
         sw = np.zeros((max(cap, 1), 2), dtype=np.uint16)
         pl = np.zeros((n, 2), dtype=np.uint16)
         b.layers.append(lr)
         b.swaps.append(sw)
         b.places.append(pl)
         r = b.res[i]
-        r.layers = lr.ctypes.data
+        if lr is not None:
+            r.layers = lr.ctypes.data
+        else:
+            ln = np.zeros(max(nl, 1), dtype=np.uint16)
+            b.lns.append(ln)
+            r.layer_n_swaps = ln.ctypes.data
         r.swaps = sw.ctypes.data
         r.swap_capacity = cap
         r.placements = pl.ctypes.data
@@ -218,7 +232,8 @@ def unpack(b: BatchBuffers) -> list:
         outs.append(RouteOutput(
             status=int(r.status), n_layers_done=int(r.n_layers_done),
             expanded_nodes=int(r.expanded_nodes), generated_nodes=int(r.generated_nodes),
-            layers=b.layers[i][:nl],
+            layers=b.layers[i][:nl] if b.layers[i] is not None else None,
+            layer_n_swaps=b.lns[i][:nl] if b.lns else None,
             swaps=b.swaps[i][: min(int(r.n_swaps_total), len(b.swaps[i]))],
             placements=b.places[i][: int(r.n_placements_total)],
             final_qubits=b.fq[i], final_locations=b.fl[i], start_locations=b.sl[i],
@@ -242,12 +257,12 @@ class CudaBackend:
 
 
 def route_batch(backend, n: int, cfg: QmgConfig, items, want_layer_qubits=False,
-                options=None, max_retries=6) -> list:
+                options=None, max_retries=6, lean=False) -> list:
     """Route `items` (RouteItem) and return one RouteOutput per item.  Swap
     buffers that turn out too small are grown and the batch is re-run."""
     cap = None
     for _ in range(max_retries):
-        b = pack(n, items, want_layer_qubits, cap)
+        b = pack(n, items, want_layer_qubits, cap, lean)
         if options is not None:
             backend.route(cfg, b, options)
         else:

@@ -144,7 +144,8 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     I.finalL = r.final_locations;
     I.startL = r.start_locations;
     I.layerQ = r.layer_qubits;
-    uint32_t summary[4] = {0, 0, 0, 0};
+    uint32_t summary[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    I.layerNSwaps = r.layer_n_swaps;
     uint64_t counters[2] = {0, 0};
     I.summary = summary;
     I.counters = counters;
