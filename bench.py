@@ -275,7 +275,7 @@ def main():
     # e2e: the C-ABI call a host makes, host buffers in and out
     e2e_ms = []
     for i in range(2 + args.steps):
-        b2 = routing.pack(n, items)
+        b2 = routing.pack(n, items, lean=True)
         st2 = _abi.QmgRouteStats()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -318,7 +318,10 @@ def main():
         "e2e": {"value": exp_all * len(e2e_ms) / t_e2e, "unit": "nodes/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": 1e3 * t_e2e / len(e2e_ms),
-                "circuits_per_s": inst_all * len(e2e_ms) / t_e2e},
+                "circuits_per_s": inst_all * len(e2e_ms) / t_e2e,
+                "outputs": "per-layer SWAP counts + SWAP list + layouts (lean results)",
+                "last_call_ms": {"stage_h2d": float(st2.h2d_ms), "kernel": float(st2.kernel_ms),
+                                 "d2h_scatter": float(st2.d2h_ms)}},
         "gpu_launches": args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None,

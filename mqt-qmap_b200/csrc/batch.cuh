@@ -1,0 +1,620 @@
+// batch.cuh - routing batches: staging of the caller's host buffers into one
+// pinned input arena (one H2D copy), launch of route_kernel<H>, and the
+// two-phase D2H of the results (summary first, then only the bytes in use).
+// Included by api.cu after the qmg_arch definition.
+#pragma once
+
+#include <chrono>
+#include <memory>
+#include <mutex>
+
+#include "staging.hpp"
+
+using qmg_workspace = qmg::Workspace;
+
+struct qmg_batch {
+  const qmg_arch* arch = nullptr;
+  CfgView cfg{};
+  size_t nInst = 0;
+  int n = 0;
+  bool wantLayers = false, wantLayerQ = false, wantLayerNS = false;
+  std::vector<uint32_t> nLayers, swapCap;
+  std::vector<uint64_t> layerOff, swapOff;
+  uint64_t totLayers = 0, totSwapCap = 0;
+  std::unique_ptr<qmg_workspace> ws;
+  // output arena offsets (bytes)
+  size_t oSummary = 0, oCounters = 0, oFinalQ = 0, oFinalL = 0, oStartL = 0,
+         oPlaces = 0, oSmallEnd = 0, oLayerNS = 0, oLayers = 0, oLayerQ = 0,
+         oSwapsPacked = 0, oSwapsWork = 0, oSwapCounter = 0, outSize = 0;
+  // input arena offsets of what the launch needs
+  size_t iInst = 0, iOrder = 0, iMem = 0, iTicket = 0, inSize = 0;
+  size_t tableOff = 0, tableBytes = 0;
+  uint32_t grid = 0, poolNodes = 0;
+  SmemLayout sl{};
+  size_t smemBytes = 0;
+  uint64_t h2dBytes = 0;
+  float h2dMs = 0.F;
+  uint32_t launches = 0;
+  ~qmg_batch();
+};
+
+namespace {
+
+std::mutex gWsMutex;
+
+std::unique_ptr<qmg_workspace> takeWorkspace(const qmg_arch* a) {
+  std::lock_guard<std::mutex> lk(gWsMutex);
+  if (a->wsCache) {
+    return std::move(a->wsCache);
+  }
+  return std::make_unique<qmg_workspace>();
+}
+void giveWorkspace(const qmg_arch* a, std::unique_ptr<qmg_workspace> ws) {
+  std::lock_guard<std::mutex> lk(gWsMutex);
+  if (!a->wsCache) {
+    a->wsCache = std::move(ws);
+  }
+}
+
+struct CircKey {
+  const void* a;
+  const void* b;
+  const void* c;
+  const void* d;
+  uint32_t nl;
+  bool operator<(const CircKey& o) const {
+    return std::tie(a, b, c, d, nl) < std::tie(o.a, o.b, o.c, o.d, o.nl);
+  }
+};
+
+}  // namespace
+
+qmg_batch::~qmg_batch() {
+  if (ws && arch != nullptr) {
+    giveWorkspace(arch, std::move(ws));
+  }
+}
+
+namespace {
+
+template <class T> T* at(uint8_t* base, size_t off) {
+  return reinterpret_cast<T*>(base + off);
+}
+
+int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
+                const qmg_instance* instances, const qmg_route_options* opt,
+                const qmg_route_result* capacities, qmg_batch** out) {
+  if (arch == nullptr || cfg == nullptr || out == nullptr ||
+      (nInst > 0 && instances == nullptr)) {
+    return fail(QMG_BAD_ARG, "null argument");
+  }
+  if (const char* msg = checkConfig(*cfg, arch->fidelity)) {
+    return fail(QMG_BAD_ARG, msg);
+  }
+  if (cfg->nr_lookaheads > (1U << 20)) {
+    return fail(QMG_BAD_ARG, "nr_lookaheads too large");
+  }
+  if (int rc = selectDevice(arch->device)) {
+    return rc;
+  }
+  auto b = std::make_unique<qmg_batch>();
+  b->arch = arch;
+  b->cfg = toCfgView(*cfg);
+  b->nInst = nInst;
+  const int n = arch->topo.n;
+  b->n = n;
+  b->ws = takeWorkspace(arch);
+  qmg_workspace& W = *b->ws;
+  cudaStream_t s = arch->stream;
+  const auto t0 = std::chrono::steady_clock::now();
+  const bool fid = b->cfg.fidelityAware != 0;
+
+  // ---- unique circuits (instances that point at the same layers share one)
+  std::map<CircKey, uint32_t> seen;
+  std::vector<CircSlot> circs;
+  std::vector<const qmg_layers*> circSrc;
+  std::vector<uint32_t> circOf(nInst);
+  size_t sumOff = 0, sumL = 0, sumG2 = 0, sumG1 = 0, sumCons = 0;
+  for (size_t i = 0; i < nInst; ++i) {
+    const qmg_layers& L = instances[i].layers;
+    if (L.n_layers > 0 &&
+        (L.gate2q_offsets == nullptr ||
+         (L.gates2q == nullptr && L.gate2q_offsets[L.n_layers] > 0) ||
+         (L.gate1q_offsets != nullptr && L.gates1q == nullptr &&
+          L.gate1q_offsets[L.n_layers] > 0))) {
+      return fail(QMG_BAD_ARG, "instance without layers");
+    }
+    const CircKey key{L.gate2q_offsets, L.gates2q, L.gate1q_offsets, L.gates1q,
+                      L.n_layers};
+    auto it = seen.find(key);
+    if (it == seen.end()) {
+      CircSlot c;
+      c.nLayers = L.n_layers;
+      c.nLogical = L.n_logical;
+      c.nG2 = L.n_layers > 0 ? L.gate2q_offsets[L.n_layers] : 0;
+      c.nG1 = (L.n_layers > 0 && L.gate1q_offsets != nullptr)
+                  ? L.gate1q_offsets[L.n_layers]
+                  : 0;
+      c.offOff = sumOff;
+      c.layerOff = sumL;
+      c.g2Off = sumG2;
+      c.g1Off = sumG1;
+      c.consOff = sumCons;
+      sumOff += static_cast<size_t>(L.n_layers) + 1;
+      sumL += L.n_layers;
+      sumG2 += c.nG2;
+      sumG1 += c.nG1;
+      sumCons += 2 * c.nG2 + c.nG1;
+      it = seen.emplace(key, static_cast<uint32_t>(circs.size())).first;
+      circs.push_back(c);
+      circSrc.push_back(&L);
+    }
+    circOf[i] = it->second;
+  }
+
+  // ---- per-instance sizes
+  b->nLayers.resize(nInst);
+  b->layerOff.resize(nInst);
+  b->swapCap.resize(nInst);
+  b->swapOff.resize(nInst);
+  for (size_t i = 0; i < nInst; ++i) {
+    const auto& c = circs[circOf[i]];
+    b->nLayers[i] = c.nLayers;
+    b->layerOff[i] = b->totLayers;
+    b->totLayers += c.nLayers;
+    uint32_t cap = 4U * c.nLayers + 256U;
+    if (capacities != nullptr) {
+      if (capacities[i].swaps != nullptr) {
+        cap = capacities[i].swap_capacity;
+      }
+      b->wantLayers = b->wantLayers || capacities[i].layers != nullptr;
+      b->wantLayerQ = b->wantLayerQ || capacities[i].layer_qubits != nullptr;
+      b->wantLayerNS = b->wantLayerNS || capacities[i].layer_n_swaps != nullptr;
+    }
+    b->swapCap[i] = cap;
+    b->swapOff[i] = b->totSwapCap;
+    b->totSwapCap += cap;
+  }
+  if (capacities == nullptr) {
+    b->wantLayers = true;  // device-resident batches keep the full records
+  }
+  if (b->totLayers > 0xFFFFFFF0ULL || b->totSwapCap > 0x3FFFFFF0ULL) {
+    return fail(QMG_BAD_ARG, "batch too large");
+  }
+  if (capacities == nullptr) {
+    b->wantLayerNS = true;
+  }
+
+  // ---- launch geometry
+  cudaDeviceProp prop{};
+  CU(cudaGetDeviceProperties(&prop, arch->device));
+  b->sl = smemLayout(n);
+  b->smemBytes = static_cast<size_t>(b->sl.bytesPerWarp) * kWarpsPerCta;
+  if (b->smemBytes > prop.sharedMemPerBlockOptin) {
+    return fail(QMG_BAD_ARG, "architecture too large for the shared-memory "
+                             "working set of one search");
+  }
+  uint32_t warpsPerSm = (opt != nullptr && opt->searches_per_sm != 0)
+                            ? opt->searches_per_sm
+                            : 32U;
+  warpsPerSm = std::max<uint32_t>(kWarpsPerCta,
+                                  warpsPerSm / kWarpsPerCta * kWarpsPerCta);
+  while (warpsPerSm > kWarpsPerCta &&
+         (b->smemBytes + 1024) * (warpsPerSm / kWarpsPerCta) >
+             prop.sharedMemPerMultiprocessor) {
+    warpsPerSm -= kWarpsPerCta;
+  }
+  const uint32_t maxCtas = static_cast<uint32_t>(prop.multiProcessorCount) *
+                           (warpsPerSm / kWarpsPerCta);
+  const uint32_t needCtas = static_cast<uint32_t>(
+      std::max<size_t>(1, (nInst + kWarpsPerCta - 1) / kWarpsPerCta));
+  b->grid = std::min(maxCtas, needCtas);
+  const uint32_t nWarps = b->grid * kWarpsPerCta;
+  const uint32_t recBytes =
+      static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
+  uint32_t poolNodes = (opt != nullptr) ? opt->pool_nodes : 0U;
+  if (poolNodes == 0) {
+    size_t freeB = 0, totalB = 0;
+    CU(cudaMemGetInfo(&freeB, &totalB));
+    freeB += W.work.cap;  // our own cached arena counts as available
+    const size_t budget = std::min<size_t>(freeB / 2, 16ULL << 30);
+    const size_t perNode = recBytes + sizeof(OpenEntry) + 4 * sizeof(uint64_t);
+    size_t pn = budget / (static_cast<size_t>(nWarps) * perNode);
+    pn = std::min<size_t>(pn, 1U << 18);
+    pn = std::max<size_t>(pn, 1024);
+    poolNodes = static_cast<uint32_t>(pn);
+  }
+  b->poolNodes = poolNodes;
+  uint32_t tableSize = 1;
+  while (tableSize < 2 * poolNodes) {
+    tableSize <<= 1;
+  }
+
+  // ---- input arena layout
+  Layout li;
+  const size_t sG2Off = li.add(sumOff * 4), sG1Off = li.add(sumOff * 4),
+               sConsOff = li.add(sumOff * 4), sG2 = li.add(sumG2 * sizeof(Gate2)),
+               sG1 = li.add(sumG1 * sizeof(Gate1)), sCons = li.add(sumCons * 2),
+               sTwoQ = li.add(sumL * 4), sFirst = li.add(sumL * 4),
+               sSplit = li.add(sumL), sInit = li.add(nInst * n * 2),
+               sFactors = li.add(static_cast<size_t>(cfg->nr_lookaheads) * 8);
+  b->iInst = li.add(nInst * sizeof(InstView));
+  b->iOrder = li.add(nInst * 4);
+  b->iMem = li.add(static_cast<size_t>(nWarps) * sizeof(SearchMem));
+  b->inSize = li.size;
+
+  // ---- output arena layout
+  Layout lo;
+  b->oSwapCounter = lo.add(16);  // [0] packed-SWAP counter, [1] ticket
+  b->oSummary = lo.add(nInst * 8 * 4);
+  b->oCounters = lo.add(nInst * 2 * 8);
+  b->oFinalQ = lo.add(nInst * n * 2);
+  b->oFinalL = lo.add(nInst * n * 2);
+  b->oStartL = lo.add(nInst * n * 2);
+  b->oPlaces = lo.add(nInst * n * 4);
+  b->oSmallEnd = lo.size;
+  b->oLayerNS = lo.add(b->wantLayerNS ? b->totLayers * 2 : 0);
+  b->oLayers = lo.add(b->wantLayers ? b->totLayers * sizeof(LayerOut) : 0);
+  b->oLayerQ = lo.add(b->wantLayerQ ? b->totLayers * n * 2 : 0);
+  b->oSwapsPacked = lo.add(b->totSwapCap * 4);
+  const size_t pinnedOut = lo.size;
+  b->oSwapsWork = lo.add(b->totSwapCap * 4);
+  b->outSize = lo.size;
+
+  // ---- work arena layout
+  Layout lw;
+  const size_t wPool = lw.add(static_cast<size_t>(nWarps) * poolNodes * recBytes);
+  const size_t wOpen =
+      lw.add(static_cast<size_t>(nWarps) * poolNodes * sizeof(OpenEntry));
+  const size_t wTable = lw.add(static_cast<size_t>(nWarps) * tableSize * 8);
+  b->tableOff = wTable;
+  b->tableBytes = static_cast<size_t>(nWarps) * tableSize * 8;
+
+  if (!W.hin.ensure(b->inSize) || !W.hout.ensure(pinnedOut)) {
+    return fail(QMG_OOM, "pinned host allocation failed");
+  }
+  CU(W.in.ensure(b->inSize));
+  CU(W.out.ensure(b->outSize));
+  uint8_t* H = W.hin.p;
+  uint8_t* D = W.in.p;
+
+  // ---- flatten the circuits into the pinned arena (host threads)
+  std::atomic<int> bad{0};
+  parallelFor(circs.size(), 16, [&](size_t ci) {
+    CircSlot& c = circs[ci];
+    const qmg_layers& L = *circSrc[ci];
+    if (!flattenCircuit(
+            n, fid, L.gate2q_offsets, reinterpret_cast<const Gate2*>(L.gates2q),
+            L.gate1q_offsets, reinterpret_cast<const Gate1*>(L.gates1q), c,
+            at<uint32_t>(H, sG2Off) + c.offOff, at<Gate2>(H, sG2) + c.g2Off,
+            at<uint32_t>(H, sG1Off) + c.offOff, at<Gate1>(H, sG1) + c.g1Off,
+            at<uint32_t>(H, sConsOff) + c.offOff, at<uint16_t>(H, sCons) + c.consOff,
+            at<uint32_t>(H, sTwoQ) + c.layerOff, at<uint32_t>(H, sFirst) + c.layerOff,
+            at<uint8_t>(H, sSplit) + c.layerOff)) {
+      bad.store(1);
+    }
+  });
+  if (bad.load() != 0) {
+    return fail(QMG_BAD_ARG, "gate operand out of range");
+  }
+  uint32_t maxG = 1;
+  for (const auto& c : circs) {
+    maxG = std::max(maxG, c.maxG);
+  }
+  const size_t wNsw = lw.add(static_cast<size_t>(nWarps) * 32 * maxG * 2);
+  CU(W.work.ensure(lw.size));
+  uint8_t* Wk = W.work.p;
+  uint8_t* O = W.out.p;
+
+  // ---- factors, per-instance inputs and views
+  {
+    const std::vector<double> f = lookaheadFactors(*cfg, 1U << 20);
+    if (!f.empty()) {
+      std::memcpy(H + sFactors, f.data(), f.size() * 8);
+    }
+    b->cfg.factors = at<double>(D, sFactors);
+    b->cfg.nFactors = static_cast<uint32_t>(f.size());
+  }
+  std::atomic<int> badInit{0};
+  parallelFor(nInst, 256, [&](size_t i) {
+    const auto& c = circs[circOf[i]];
+    int16_t* init = at<int16_t>(H, sInit) + i * n;
+    if (instances[i].initial_locations != nullptr) {
+      for (int q = 0; q < n; ++q) {
+        const int16_t p = instances[i].initial_locations[q];
+        if (p < -1 || p >= n) {
+          badInit.store(1);
+        }
+        init[q] = p;
+      }
+    } else {
+      std::fill(init, init + n, static_cast<int16_t>(-1));
+    }
+    InstView& I = at<InstView>(H, b->iInst)[i];
+    std::memset(&I, 0, sizeof(I));
+    I.circ.nLayers = c.nLayers;
+    I.circ.nLogical = c.nLogical;
+    I.circ.g2Off = at<uint32_t>(D, sG2Off) + c.offOff;
+    I.circ.g2 = at<Gate2>(D, sG2) + c.g2Off;
+    I.circ.g1Off = at<uint32_t>(D, sG1Off) + c.offOff;
+    I.circ.g1 = at<Gate1>(D, sG1) + c.g1Off;
+    I.circ.consOff = at<uint32_t>(D, sConsOff) + c.offOff;
+    I.circ.cons = at<uint16_t>(D, sCons) + c.consOff;
+    I.circ.twoQ = at<uint32_t>(D, sTwoQ) + c.layerOff;
+    I.circ.firstAfter = at<uint32_t>(D, sFirst) + c.layerOff;
+    I.circ.nTwoQ = c.nTwoQ;
+    I.circ.splittable = at<uint8_t>(D, sSplit) + c.layerOff;
+    I.initLoc = at<int16_t>(D, sInit) + i * n;
+    I.passes = instances[i].bidirectional_passes;
+    I.firstLayer = instances[i].first_layer;
+    I.nRoute = instances[i].n_route_layers;
+    I.layers = b->wantLayers ? at<LayerOut>(O, b->oLayers) + b->layerOff[i]
+                             : nullptr;
+    I.layerNSwaps = b->wantLayerNS ? at<uint16_t>(O, b->oLayerNS) + b->layerOff[i]
+                                   : nullptr;
+    I.layerQ = b->wantLayerQ
+                   ? at<int16_t>(O, b->oLayerQ) + b->layerOff[i] * n
+                   : nullptr;
+    I.swaps = at<uint16_t>(O, b->oSwapsWork) + 2 * b->swapOff[i];
+    I.swapCap = b->swapCap[i];
+    I.swapsPacked = at<uint16_t>(O, b->oSwapsPacked);
+    I.swapCounter = at<uint32_t>(O, b->oSwapCounter);
+    I.places = at<uint16_t>(O, b->oPlaces) + 2 * i * n;
+    I.placeCap = static_cast<uint32_t>(n);
+    I.finalQ = at<int16_t>(O, b->oFinalQ) + i * n;
+    I.finalL = at<int16_t>(O, b->oFinalL) + i * n;
+    I.startL = at<int16_t>(O, b->oStartL) + i * n;
+    I.summary = at<uint32_t>(O, b->oSummary) + 8 * i;
+    I.counters = at<uint64_t>(O, b->oCounters) + 2 * i;
+  });
+  if (badInit.load() != 0) {
+    return fail(QMG_BAD_ARG, "initial location out of range");
+  }
+  {
+    // largest instances first
+    uint32_t* order = at<uint32_t>(H, b->iOrder);
+    std::iota(order, order + nInst, 0U);
+    bool uniform = true;
+    for (size_t i = 1; i < nInst && uniform; ++i) {
+      uniform = b->nLayers[i] == b->nLayers[0] &&
+                instances[i].bidirectional_passes ==
+                    instances[0].bidirectional_passes;
+    }
+    if (!uniform) {
+      std::stable_sort(order, order + nInst, [&](uint32_t x, uint32_t y) {
+        const uint64_t wx = static_cast<uint64_t>(b->nLayers[x]) *
+                            (1 + 2 * instances[x].bidirectional_passes);
+        const uint64_t wy = static_cast<uint64_t>(b->nLayers[y]) *
+                            (1 + 2 * instances[y].bidirectional_passes);
+        return wx > wy;
+      });
+    }
+  }
+  {
+    SearchMem* mem = at<SearchMem>(H, b->iMem);
+    for (uint32_t w = 0; w < nWarps; ++w) {
+      SearchMem& M = mem[w];
+      M.pool = Wk + wPool + static_cast<size_t>(w) * poolNodes * recBytes;
+      M.open = at<OpenEntry>(Wk, wOpen) + static_cast<size_t>(w) * poolNodes;
+      M.table = at<uint64_t>(Wk, wTable) + static_cast<size_t>(w) * tableSize;
+      M.nsw = at<uint16_t>(Wk, wNsw) + static_cast<size_t>(w) * 32 * maxG;
+      M.poolCap = poolNodes;
+      M.recBytes = recBytes;
+      M.tableMask = tableSize - 1;
+      M.stamp = 0;
+      M.maxG = maxG;
+    }
+  }
+  CU(cudaMemcpyAsync(D, H, b->inSize, cudaMemcpyHostToDevice, s));
+  CU(cudaMemsetAsync(Wk + b->tableOff, 0, b->tableBytes, s));
+  b->h2dBytes = b->inSize;
+  {
+    const int sb = static_cast<int>(b->smemBytes);
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    CU(cudaFuncSetAttribute(route_kernel<0>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<1>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<2>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<3>, attr, sb));
+    CU(cudaFuncSetAttribute(route_kernel<4>, attr, sb));
+  }
+  CU(cudaStreamSynchronize(s));
+  b->h2dMs = std::chrono::duration<float, std::milli>(
+                 std::chrono::steady_clock::now() - t0)
+                 .count();
+  *out = b.release();
+  return QMG_OK;
+}
+
+int batchRun(qmg_batch* b, qmg_route_stats* stats) {
+  if (int rc = selectDevice(b->arch->device)) {
+    return rc;
+  }
+  cudaStream_t s = b->arch->stream;
+  qmg_workspace& W = *b->ws;
+  // packed-SWAP counter and instance ticket
+  CU(cudaMemsetAsync(W.out.p + b->oSwapCounter, 0, 16, s));
+  EventTimer tm(s);
+  tm.start();
+  if (b->nInst > 0) {
+    const ArchView av = b->arch->view();
+    const uint32_t nI = static_cast<uint32_t>(b->nInst);
+    const dim3 blk(kWarpsPerCta * 32);
+    const InstView* inst = at<InstView>(W.in.p, b->iInst);
+    const uint32_t* order = at<uint32_t>(W.in.p, b->iOrder);
+    SearchMem* mem = at<SearchMem>(W.in.p, b->iMem);
+    uint32_t* ticket = at<uint32_t>(W.out.p, b->oSwapCounter) + 1;
+#define QMG_LAUNCH(HH)                                                         \
+  route_kernel<HH><<<b->grid, blk, b->smemBytes, s>>>(av, b->cfg, inst, order, \
+                                                      nI, mem, ticket, b->sl)
+    switch (b->cfg.heuristic) {
+    case 0:
+      QMG_LAUNCH(0);
+      break;
+    case 1:
+      QMG_LAUNCH(1);
+      break;
+    case 2:
+      QMG_LAUNCH(2);
+      break;
+    case 3:
+      QMG_LAUNCH(3);
+      break;
+    default:
+      QMG_LAUNCH(4);
+      break;
+    }
+#undef QMG_LAUNCH
+    CU(cudaGetLastError());
+    ++b->launches;
+  }
+  const float ms = tm.stop();
+  CU(cudaStreamSynchronize(s));
+  if (stats != nullptr) {
+    stats->kernel_ms = ms;
+    stats->h2d_ms = b->h2dMs;
+    stats->grid = b->grid;
+    stats->block = kWarpsPerCta * 32;
+    stats->h2d_bytes = b->h2dBytes;
+    stats->kernel_launches = b->launches;
+  }
+  return QMG_OK;
+}
+
+int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) {
+  if (int rc = selectDevice(b->arch->device)) {
+    return rc;
+  }
+  cudaStream_t s = b->arch->stream;
+  qmg_workspace& W = *b->ws;
+  const size_t nI = b->nInst;
+  const size_t n = static_cast<size_t>(b->n);
+  const auto t0 = std::chrono::steady_clock::now();
+  uint8_t* Hh = W.hout.p;
+  const uint8_t* O = W.out.p;
+  // phase 1: summaries, counters, layouts, placements
+  CU(cudaMemcpyAsync(Hh, O, b->oSmallEnd, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  // phase 2: per-layer outputs and the SWAPs actually produced
+  const uint32_t packed = *at<uint32_t>(Hh, b->oSwapCounter);
+  const size_t end2 = b->oSwapsPacked + static_cast<size_t>(packed) * 4;
+  if (end2 > b->oSmallEnd) {
+    CU(cudaMemcpyAsync(Hh + b->oSmallEnd, O + b->oSmallEnd, end2 - b->oSmallEnd,
+                       cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+  }
+  const uint32_t* summary = at<uint32_t>(Hh, b->oSummary);
+  const uint64_t* counters = at<uint64_t>(Hh, b->oCounters);
+  std::atomic<uint64_t> exp{0}, gen{0};
+  parallelFor(nI, 512, [&](size_t i) {
+    qmg_route_result& r = results[i];
+    r.n_swaps_total = summary[8 * i];
+    r.n_placements_total = summary[8 * i + 1];
+    r.n_layers_done = summary[8 * i + 2];
+    r.status = static_cast<int32_t>(summary[8 * i + 3]);
+    r.expanded_nodes = counters[2 * i];
+    r.generated_nodes = counters[2 * i + 1];
+    exp.fetch_add(r.expanded_nodes, std::memory_order_relaxed);
+    gen.fetch_add(r.generated_nodes, std::memory_order_relaxed);
+    const size_t nl = b->nLayers[i];
+    if (r.layers != nullptr && b->wantLayers) {
+      std::memcpy(r.layers, at<LayerOut>(Hh, b->oLayers) + b->layerOff[i],
+                  nl * sizeof(LayerOut));
+    }
+    if (r.layer_n_swaps != nullptr && b->wantLayerNS) {
+      std::memcpy(r.layer_n_swaps, at<uint16_t>(Hh, b->oLayerNS) + b->layerOff[i],
+                  nl * 2);
+    }
+    if (r.layer_qubits != nullptr && b->wantLayerQ) {
+      std::memcpy(r.layer_qubits, at<int16_t>(Hh, b->oLayerQ) + b->layerOff[i] * n,
+                  nl * n * 2);
+    }
+    if (r.swaps != nullptr) {
+      const uint32_t ns = r.n_swaps_total;
+      if (ns <= b->swapCap[i] && ns <= r.swap_capacity) {
+        std::memcpy(r.swaps,
+                    at<uint32_t>(Hh, b->oSwapsPacked) + summary[8 * i + 4],
+                    static_cast<size_t>(ns) * 4);
+      } else if (r.status == QMG_OK) {
+        r.status = QMG_BUFFER_TOO_SMALL;
+      }
+    }
+    const uint32_t np =
+        std::min<uint32_t>(r.n_placements_total, static_cast<uint32_t>(n));
+    if (r.placements != nullptr && r.placement_capacity >= np) {
+      std::memcpy(r.placements, at<uint16_t>(Hh, b->oPlaces) + 2 * i * n,
+                  static_cast<size_t>(np) * 4);
+    }
+    if (r.final_qubits != nullptr) {
+      std::memcpy(r.final_qubits, at<int16_t>(Hh, b->oFinalQ) + i * n, n * 2);
+    }
+    if (r.final_locations != nullptr) {
+      std::memcpy(r.final_locations, at<int16_t>(Hh, b->oFinalL) + i * n, n * 2);
+    }
+    if (r.start_locations != nullptr) {
+      std::memcpy(r.start_locations, at<int16_t>(Hh, b->oStartL) + i * n, n * 2);
+    }
+  });
+  if (stats != nullptr) {
+    stats->d2h_ms = std::chrono::duration<float, std::milli>(
+                        std::chrono::steady_clock::now() - t0)
+                        .count();
+    stats->d2h_bytes = std::max(end2, b->oSmallEnd);
+    stats->expanded_nodes = exp.load();
+    stats->generated_nodes = gen.load();
+  }
+  return QMG_OK;
+}
+
+}  // namespace
+
+QMG_API int qmg_batch_create(const qmg_arch* arch, const qmg_config* cfg,
+                             size_t nInstances, const qmg_instance* instances,
+                             const qmg_route_options* options,
+                             qmg_batch** out) {
+  return guarded([&] {
+    return batchCreate(arch, cfg, nInstances, instances, options, nullptr, out);
+  });
+}
+QMG_API int qmg_batch_run(qmg_batch* batch, qmg_route_stats* stats) {
+  if (batch == nullptr) {
+    return fail(QMG_BAD_ARG, "null batch");
+  }
+  return guarded([&] { return batchRun(batch, stats); });
+}
+QMG_API int qmg_batch_fetch(qmg_batch* batch, qmg_route_result* results) {
+  if (batch == nullptr || results == nullptr) {
+    return fail(QMG_BAD_ARG, "null argument");
+  }
+  return guarded([&] { return batchFetch(batch, results, nullptr); });
+}
+QMG_API void qmg_batch_destroy(qmg_batch* batch) {
+  if (batch != nullptr) {
+    cudaSetDevice(batch->arch->device);
+    delete batch;
+  }
+}
+
+QMG_API int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
+                            size_t nInstances, const qmg_instance* instances,
+                            qmg_route_result* results,
+                            const qmg_route_options* options,
+                            qmg_route_stats* stats) {
+  if (results == nullptr && nInstances > 0) {
+    return fail(QMG_BAD_ARG, "null results");
+  }
+  return guarded([&] {
+    qmg_batch* b = nullptr;
+    if (int rc = batchCreate(arch, cfg, nInstances, instances, options, results,
+                             &b)) {
+      return rc;
+    }
+    std::unique_ptr<qmg_batch> hold(b);
+    if (stats != nullptr) {
+      std::memset(stats, 0, sizeof(*stats));
+    }
+    if (int rc = batchRun(b, stats)) {
+      return rc;
+    }
+    return batchFetch(b, results, stats);
+  });
+}

@@ -9,6 +9,7 @@
 // timed.  Cost tables are INPUTS here (the table kernels exist only in CUDA).
 #define QMG_HOST_API_IMPL
 #include "../../mqt-qmap_b200/csrc/host_api.hpp"
+#include "../../mqt-qmap_b200/csrc/flatten.hpp"
 
 #include <memory>
 #include <vector>
@@ -104,12 +105,47 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
   for (size_t ii = 0; ii < nInstances; ++ii) {
     const qmg_instance& in = instances[ii];
     qmg_route_result& r = results[ii];
-    FlatCircuit fc;
-    fc.build(in.layers.n_layers, in.layers.n_logical, in.layers.gate2q_offsets,
-             reinterpret_cast<const Gate2*>(in.layers.gates2q),
-             in.layers.gate1q_offsets,
-             reinterpret_cast<const Gate1*>(in.layers.gates1q),
-             C.fidelityAware != 0);
+    // the same flattening the CUDA batches use (flatten.hpp)
+    const qmg_layers& Ly = in.layers;
+    CircSlot slot;
+    slot.nLayers = Ly.n_layers;
+    slot.nLogical = Ly.n_logical;
+    slot.nG2 = Ly.n_layers > 0 ? Ly.gate2q_offsets[Ly.n_layers] : 0;
+    slot.nG1 = (Ly.n_layers > 0 && Ly.gate1q_offsets != nullptr)
+                   ? Ly.gate1q_offsets[Ly.n_layers]
+                   : 0;
+    const size_t nLy = Ly.n_layers;
+    std::vector<uint32_t> fG2Off(nLy + 1), fG1Off(nLy + 1), fConsOff(nLy + 1),
+        fTwoQ(nLy + 1), fFirst(nLy + 1);
+    std::vector<Gate2> fG2(slot.nG2 + 1);
+    std::vector<Gate1> fG1(slot.nG1 + 1);
+    std::vector<uint16_t> fCons(2 * slot.nG2 + slot.nG1 + 1);
+    std::vector<uint8_t> fSplit(nLy + 1);
+    if (!flattenCircuit(n, C.fidelityAware != 0, Ly.gate2q_offsets,
+                        reinterpret_cast<const Gate2*>(Ly.gates2q),
+                        Ly.gate1q_offsets,
+                        reinterpret_cast<const Gate1*>(Ly.gates1q), slot,
+                        fG2Off.data(), fG2.data(), fG1Off.data(), fG1.data(),
+                        fConsOff.data(), fCons.data(), fTwoQ.data(),
+                        fFirst.data(), fSplit.data())) {
+      return fail(QMG_BAD_ARG, "gate operand out of range");
+    }
+    struct {
+      uint32_t maxG;
+    } fc{slot.maxG};
+    CircView cv{};
+    cv.nLayers = slot.nLayers;
+    cv.nLogical = slot.nLogical;
+    cv.g2Off = fG2Off.data();
+    cv.g2 = fG2.data();
+    cv.g1Off = fG1Off.data();
+    cv.g1 = fG1.data();
+    cv.consOff = fConsOff.data();
+    cv.cons = fCons.data();
+    cv.twoQ = fTwoQ.data();
+    cv.firstAfter = fFirst.data();
+    cv.nTwoQ = slot.nTwoQ;
+    cv.splittable = fSplit.data();
     std::vector<uint16_t> nsw(static_cast<size_t>(fc.maxG) + 1);
     SearchMem M{};
     M.pool = reinterpret_cast<uint8_t*>(poolStore.data());
@@ -130,7 +166,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     S.ch = ch.data();
     S.lookPen = lookPen.data();
     InstView I{};
-    I.circ = fc.view();
+    I.circ = cv;
     I.initLoc = in.initial_locations;
     I.passes = in.bidirectional_passes;
     I.firstLayer = in.first_layer;
