@@ -306,6 +306,12 @@ def main():
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f)["route_kernel"]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        pass
     avg_launch_s = (sum(kernel_ms) / len(kernel_ms)) / 1e3
     abytes = algorithmic_bytes(n, exp, gen)
     achieved = abytes / avg_launch_s / 1e9
@@ -324,7 +330,7 @@ def main():
                                  "d2h_scatter": float(st2.d2h_ms)}},
         "gpu_launches": args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                      "kernel": "route_kernel", "algorithmic_bytes_per_launch": abytes},
         "cpu_baseline": cpu_base,

@@ -352,6 +352,7 @@ struct qmg_arch {
   float buildMs = 0.F;
   // buffers of the last routing batch, reused by the next one (batch.cuh)
   mutable std::unique_ptr<Workspace> wsCache;
+  DeviceLimits limits;
   ~qmg_arch() {
     wsCache.reset();
     if (stream != nullptr) {
@@ -390,6 +391,13 @@ QMG_API int qmg_arch_create(uint16_t n, const uint16_t* edges, size_t nEdges,
     a->device = device;
     a->topo.build(n, edges, nEdges);
     CU(cudaStreamCreate(&a->stream));
+    {
+      cudaDeviceProp prop{};
+      CU(cudaGetDeviceProperties(&prop, device));
+      a->limits.multiProcessorCount = prop.multiProcessorCount;
+      a->limits.sharedMemPerBlockOptin = prop.sharedMemPerBlockOptin;
+      a->limits.sharedMemPerMultiprocessor = prop.sharedMemPerMultiprocessor;
+    }
     a->td.upload(a->topo);
     const size_t nn = static_cast<size_t>(n) * n;
     // Architecture::createDistanceTable :201-230

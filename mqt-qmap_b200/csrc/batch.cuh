@@ -5,8 +5,10 @@
 #pragma once
 
 #include <chrono>
+#include <cstdlib>
 #include <memory>
 #include <mutex>
+#include <unordered_map>
 
 #include "staging.hpp"
 
@@ -42,6 +44,32 @@ namespace {
 
 std::mutex gWsMutex;
 
+// QMAP_B200_TRACE=1 prints the host-side stage times of every batch
+bool traceOn() {
+  static const bool on = std::getenv("QMAP_B200_TRACE") != nullptr;
+  return on;
+}
+struct StageClock {
+  std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+  std::string log;
+  void mark(const char* what) {
+    if (!traceOn()) {
+      return;
+    }
+    const auto now = std::chrono::steady_clock::now();
+    char buf[64];
+    std::snprintf(buf, sizeof(buf), " %s=%.2fms", what,
+                  std::chrono::duration<double, std::milli>(now - t).count());
+    log += buf;
+    t = now;
+  }
+  void flush(const char* who) {
+    if (traceOn()) {
+      std::fprintf(stderr, "[qmap_b200] %s:%s\n", who, log.c_str());
+    }
+  }
+};
+
 std::unique_ptr<qmg_workspace> takeWorkspace(const qmg_arch* a) {
   std::lock_guard<std::mutex> lk(gWsMutex);
   if (a->wsCache) {
@@ -62,8 +90,17 @@ struct CircKey {
   const void* c;
   const void* d;
   uint32_t nl;
-  bool operator<(const CircKey& o) const {
-    return std::tie(a, b, c, d, nl) < std::tie(o.a, o.b, o.c, o.d, o.nl);
+  bool operator==(const CircKey& o) const {
+    return a == o.a && b == o.b && c == o.c && d == o.d && nl == o.nl;
+  }
+};
+struct CircKeyHash {
+  size_t operator()(const CircKey& k) const {
+    uint64_t h = reinterpret_cast<uintptr_t>(k.a) * 0x9E3779B97F4A7C15ULL;
+    h ^= reinterpret_cast<uintptr_t>(k.b) + 0xBF58476D1CE4E5B9ULL + (h << 6) +
+         (h >> 2);
+    h ^= reinterpret_cast<uintptr_t>(k.c) * 0x94D049BB133111EBULL + (h >> 29);
+    return static_cast<size_t>(h ^ (h >> 32) ^ k.nl);
   }
 };
 
@@ -108,9 +145,11 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   cudaStream_t s = arch->stream;
   const auto t0 = std::chrono::steady_clock::now();
   const bool fid = b->cfg.fidelityAware != 0;
+  StageClock sc;
 
   // ---- unique circuits (instances that point at the same layers share one)
-  std::map<CircKey, uint32_t> seen;
+  std::unordered_map<CircKey, uint32_t, CircKeyHash> seen;
+  seen.reserve(nInst * 2);
   std::vector<CircSlot> circs;
   std::vector<const qmg_layers*> circSrc;
   std::vector<uint32_t> circOf(nInst);
@@ -152,6 +191,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     circOf[i] = it->second;
   }
 
+  sc.mark("dedupe");
   // ---- per-instance sizes
   b->nLayers.resize(nInst);
   b->layerOff.resize(nInst);
@@ -185,9 +225,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     b->wantLayerNS = true;
   }
 
+  sc.mark("sizes");
   // ---- launch geometry
-  cudaDeviceProp prop{};
-  CU(cudaGetDeviceProperties(&prop, arch->device));
+  const DeviceLimits& prop = arch->limits;
   b->sl = smemLayout(n);
   b->smemBytes = static_cast<size_t>(b->sl.bytesPerWarp) * kWarpsPerCta;
   if (b->smemBytes > prop.sharedMemPerBlockOptin) {
@@ -214,10 +254,12 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
   uint32_t poolNodes = (opt != nullptr) ? opt->pool_nodes : 0U;
   if (poolNodes == 0) {
-    size_t freeB = 0, totalB = 0;
-    CU(cudaMemGetInfo(&freeB, &totalB));
-    freeB += W.work.cap;  // our own cached arena counts as available
-    const size_t budget = std::min<size_t>(freeB / 2, 16ULL << 30);
+    if (W.memBudget == 0) {
+      size_t freeB = 0, totalB = 0;
+      CU(cudaMemGetInfo(&freeB, &totalB));
+      W.memBudget = std::min<size_t>(freeB / 2, 16ULL << 30);
+    }
+    const size_t budget = W.memBudget;
     const size_t perNode = recBytes + sizeof(OpenEntry) + 4 * sizeof(uint64_t);
     size_t pn = budget / (static_cast<size_t>(nWarps) * perNode);
     pn = std::min<size_t>(pn, 1U << 18);
@@ -230,6 +272,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     tableSize <<= 1;
   }
 
+  sc.mark("geometry");
   // ---- input arena layout
   Layout li;
   const size_t sG2Off = li.add(sumOff * 4), sG1Off = li.add(sumOff * 4),
@@ -278,6 +321,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   uint8_t* H = W.hin.p;
   uint8_t* D = W.in.p;
 
+  sc.mark("alloc");
   // ---- flatten the circuits into the pinned arena (host threads)
   std::atomic<int> bad{0};
   parallelFor(circs.size(), 16, [&](size_t ci) {
@@ -297,6 +341,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   if (bad.load() != 0) {
     return fail(QMG_BAD_ARG, "gate operand out of range");
   }
+  sc.mark("flatten");
   uint32_t maxG = 1;
   for (const auto& c : circs) {
     maxG = std::max(maxG, c.maxG);
@@ -306,6 +351,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   uint8_t* Wk = W.work.p;
   uint8_t* O = W.out.p;
 
+  sc.mark("work-alloc");
   // ---- factors, per-instance inputs and views
   {
     const std::vector<double> f = lookaheadFactors(*cfg, 1U << 20);
@@ -405,6 +451,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       M.maxG = maxG;
     }
   }
+  sc.mark("views");
   CU(cudaMemcpyAsync(D, H, b->inSize, cudaMemcpyHostToDevice, s));
   CU(cudaMemsetAsync(Wk + b->tableOff, 0, b->tableBytes, s));
   b->h2dBytes = b->inSize;
@@ -417,7 +464,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     CU(cudaFuncSetAttribute(route_kernel<3>, attr, sb));
     CU(cudaFuncSetAttribute(route_kernel<4>, attr, sb));
   }
+  sc.mark("attrs");
   CU(cudaStreamSynchronize(s));
+  sc.mark("h2d-sync");
+  sc.flush("batch_create");
   b->h2dMs = std::chrono::duration<float, std::milli>(
                  std::chrono::steady_clock::now() - t0)
                  .count();
@@ -490,10 +540,12 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
   const size_t n = static_cast<size_t>(b->n);
   const auto t0 = std::chrono::steady_clock::now();
   uint8_t* Hh = W.hout.p;
+  StageClock sc;
   const uint8_t* O = W.out.p;
   // phase 1: summaries, counters, layouts, placements
   CU(cudaMemcpyAsync(Hh, O, b->oSmallEnd, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamSynchronize(s));
+  sc.mark("d2h-small");
   // phase 2: per-layer outputs and the SWAPs actually produced
   const uint32_t packed = *at<uint32_t>(Hh, b->oSwapCounter);
   const size_t end2 = b->oSwapsPacked + static_cast<size_t>(packed) * 4;
@@ -502,6 +554,7 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
                        cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
   }
+  sc.mark("d2h-bulk");
   const uint32_t* summary = at<uint32_t>(Hh, b->oSummary);
   const uint64_t* counters = at<uint64_t>(Hh, b->oCounters);
   std::atomic<uint64_t> exp{0}, gen{0};
@@ -554,6 +607,8 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
       std::memcpy(r.start_locations, at<int16_t>(Hh, b->oStartL) + i * n, n * 2);
     }
   });
+  sc.mark("scatter");
+  sc.flush("batch_fetch");
   if (stats != nullptr) {
     stats->d2h_ms = std::chrono::duration<float, std::milli>(
                         std::chrono::steady_clock::now() - t0)

@@ -81,6 +81,15 @@ struct DevArena {
 struct Workspace {
   DevArena in, out, work;
   PinnedBuf hin, hout;
+  size_t memBudget = 0;  // device bytes the search pools may take
+};
+
+// the few cudaDeviceProp fields the launch geometry needs (the query is slow,
+// so it is made once per Architecture)
+struct DeviceLimits {
+  int multiProcessorCount = 0;
+  size_t sharedMemPerBlockOptin = 0;
+  size_t sharedMemPerMultiprocessor = 0;
 };
 
 }  // namespace qmg

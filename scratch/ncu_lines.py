@@ -7,7 +7,7 @@ tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, stdout=subprocess.DEVNULL)
 cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
 dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cub)], capture_output=True, text=True).stdout.split("\n")
-start = [i for i, l in enumerate(dis) if ".text._ZN3qmg12route_kernel" in l and ".section" in l][0]
+start = [i for i, l in enumerate(dis) if ".text._ZN3qmg12route_kernelILi0E" in l and ".section" in l][0]
 cur = None; addr2line = {}
 pat = re.compile(r"/\*([0-9a-f]{4,})\*/")
 for l in dis[start:]:
@@ -35,3 +35,37 @@ src = open(os.path.join(os.path.dirname(os.path.abspath(lib)), "route_core.hpp")
 for k, n in sagg.most_common(top):
     txt = src[k[1] - 1].strip()[:60] if k and k[0] == "route_core.hpp" else ""
     print(k, "samp%", round(100 * n / stot, 1), "inst%", round(100 * agg[k] / tot, 1), "static", static[k], dict(stl[k].most_common(2)), "|", txt)
+
+# per-function aggregation (enclosing QMG_HD definition of each line)
+import bisect
+defs = [(i + 1, re.sub(r".*?([A-Za-z0-9_]+)\(.*", r"\1", l)) for i, l in enumerate(src) if re.match(r"\s*QMG_(HD|D) ", l)]
+dl = [d[0] for d in defs]
+fa = collections.Counter(); fs = collections.Counter(); fst = collections.defaultdict(collections.Counter)
+for k, nI in agg.items():
+    if k and k[0] == "route_core.hpp":
+        j = bisect.bisect_right(dl, k[1]) - 1
+        name = defs[j][1] if j >= 0 else "?"
+    else:
+        name = str(k[0]) if k else "none"
+    fa[name] += nI; fs[name] += sagg[k]
+    for kk, vv in stl[k].items(): fst[name][kk] += vv
+print("---- per function")
+for name, nI in fa.most_common(30):
+    print(f"{name:24s} inst% {100*nI/tot:5.1f}  samp% {100*fs[name]/stot:5.1f}", dict(fst[name].most_common(3)))
+# hot code footprint per function: static instructions executed at least once
+ff = collections.Counter(); fh = collections.Counter()
+thr = tot / 1e5
+for r in data:
+    key = addr2line.get(int(r[iad], 16) - base)
+    nI = int(r[ia] or 0)
+    if key and key[0] == "route_core.hpp":
+        j = bisect.bisect_right(dl, key[1]) - 1
+        name = defs[j][1] if j >= 0 else "?"
+    else:
+        name = str(key[0]) if key else "none"
+    if nI > 0: ff[name] += 1
+    if nI > thr: fh[name] += 1
+print("---- executed static instr per function (touched / hot>1e-5 of total)")
+for name, c in ff.most_common(30):
+    print(f"{name:24s} touched {c:5d} ({c*16/1024:5.1f} KB)  hot {fh[name]:5d}")
+print("total touched", sum(ff.values()), "hot", sum(fh.values()))
