@@ -42,6 +42,13 @@ def instance_perm(seed: int) -> np.ndarray:
     return np.random.default_rng(1000003 + seed).permutation(16)
 
 
+def shard_seeds(rank: int, world: int, batch: int) -> range:
+    """Instances of rank `rank`: every rank routes `batch` instances of its own
+    (weak scaling, no data-path collective); seeds are disjoint across ranks."""
+    assert 0 <= rank < world
+    return range(rank * batch, (rank + 1) * batch)
+
+
 def relabel_arrays(c, t, perm):
     perm = np.asarray(perm, dtype=np.int32)
     return (np.where(c >= 0, perm[np.maximum(c, 0)], -1).astype(np.int32),
@@ -226,7 +233,7 @@ def main():
     base = qcirc.load_qasm(QASM)
     cfg = routing.make_config(initial_layout="identity")
     B = args.batch
-    seeds = range(rank * B, (rank + 1) * B)
+    seeds = shard_seeds(rank, world, B)
     items = []
     c0, t0_ = base.gate_arrays()
     for s in seeds:

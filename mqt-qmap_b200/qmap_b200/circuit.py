@@ -49,10 +49,40 @@ class Circuit:
         self.gate("h", q)
 
     def used_qubits(self) -> list:
+        """Qubits that are not idle: touched by a gate or measured."""
         used = set()
         for op in self.ops:
             used.update(op.qubits)
+        used.update(q for q, _ in self.measurements)
         return sorted(used)
+
+    def mapper_view(self, n_physical: int):
+        """What the reference mapper makes of this circuit before routing:
+        (control, target, identity_locations).
+
+        Mapper's constructor strips idle qubits (src/sc/Mapper.cpp:44-53;
+        mqt-core's stripIdleQubits(force) moves the logical indices above a
+        removed qubit down by one) and createLayers reads every gate operand
+        through `initialLayout` (Mapper.cpp:166-172), so operand q becomes the
+        rank of q among the used qubits.  InitialLayout::Identity then places
+        logical i on physical i for every *original* used index i
+        (HeuristicMapper.cpp:176-183) - with an idle qubit in the middle that
+        leaves the highest logical qubit(s) unplaced until their first gate,
+        which the golden layouts of 4gt11_84 in the reference's
+        test_heuristic.cpp pin."""
+        used = self.used_qubits()
+        rank = {q: i for i, q in enumerate(used)}
+        c, t = self.gate_arrays()
+        lut = np.full(max(self.n_qubits, 1), -1, dtype=np.int32)
+        for q, i in rank.items():
+            lut[q] = i
+        t = lut[t]
+        c = np.where(c >= 0, lut[np.maximum(c, 0)], -1).astype(np.int32)
+        identity = np.full(n_physical, -1, dtype=np.int16)
+        for q in used:
+            if q < n_physical:
+                identity[q] = q
+        return c, t.astype(np.int32), identity
 
     def gate_arrays(self):
         """(control, target) int32 arrays; control = -1 for 1q gates."""

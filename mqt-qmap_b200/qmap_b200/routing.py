@@ -171,11 +171,14 @@ class BatchBuffers:
     lq: list = field(default_factory=list)
     lns: list = field(default_factory=list)
     keep: list = field(default_factory=list)
+    layer_cap: list = field(default_factory=list)  # per-instance rows of layers/lq/lns
 
 
-def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False) -> BatchBuffers:
+def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False,
+         extra_layers=0) -> BatchBuffers:
     """lean: no per-layer qmg_layer_result records, only the compact per-layer
-    SWAP counts (what circuit emission needs)."""
+    SWAP counts (what circuit emission needs).  extra_layers: additional rows
+    in the per-layer outputs for backends that split layers themselves."""
     nI = len(items)
     b = BatchBuffers(n=n, items=list(items))
     b.inst = (QmgInstance * nI)()
@@ -186,6 +189,8 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False)
     for i, it in enumerate(items):
         lay = it.circuit.layers
         nl = int(lay.n_layers)
+        cap_l = max(nl + extra_layers, 1)
+        b.layer_cap.append(cap_l)
         ins = b.inst[i]
         ins.layers = lay
         if it.initial_locations is not None:
@@ -196,8 +201,8 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False)
         ins.bidirectional_passes = it.bidirectional_passes
         ins.first_layer = it.first_layer
         ins.n_route_layers = it.n_route_layers
-        cap = swap_capacity if swap_capacity is not None else 4 * nl + 256
-        lr = None if lean else np.zeros(max(nl, 1), dtype=LAYER_RESULT_DTYPE)
+        cap = swap_capacity if swap_capacity is not None else 4 * cap_l + 256
+        lr = None if lean else np.zeros(cap_l, dtype=LAYER_RESULT_DTYPE)
         sw = np.zeros((max(cap, 1), 2), dtype=np.uint16)
         pl = np.zeros((n, 2), dtype=np.uint16)
         b.layers.append(lr)
@@ -207,7 +212,7 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False)
         if lr is not None:
             r.layers = lr.ctypes.data
         else:
-            ln = np.zeros(max(nl, 1), dtype=np.uint16)
+            ln = np.zeros(cap_l, dtype=np.uint16)
             b.lns.append(ln)
             r.layer_n_swaps = ln.ctypes.data
         r.swaps = sw.ctypes.data
@@ -218,7 +223,7 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False)
         r.final_locations = b.fl[i].ctypes.data
         r.start_locations = b.sl[i].ctypes.data
         if want_layer_qubits:
-            lq = np.full((max(nl, 1), n), -1, dtype=np.int16)
+            lq = np.full((cap_l, n), -1, dtype=np.int16)
             b.lq.append(lq)
             r.layer_qubits = lq.ctypes.data
     return b
@@ -228,7 +233,7 @@ def unpack(b: BatchBuffers) -> list:
     outs = []
     for i, it in enumerate(b.items):
         r = b.res[i]
-        nl = it.circuit.n_layers
+        nl = min(max(it.circuit.n_layers, int(r.n_layers_done)), b.layer_cap[i])
         outs.append(RouteOutput(
             status=int(r.status), n_layers_done=int(r.n_layers_done),
             expanded_nodes=int(r.expanded_nodes), generated_nodes=int(r.generated_nodes),
@@ -257,12 +262,12 @@ class CudaBackend:
 
 
 def route_batch(backend, n: int, cfg: QmgConfig, items, want_layer_qubits=False,
-                options=None, max_retries=6, lean=False) -> list:
+                options=None, max_retries=6, lean=False, extra_layers=0) -> list:
     """Route `items` (RouteItem) and return one RouteOutput per item.  Swap
     buffers that turn out too small are grown and the batch is re-run."""
     cap = None
     for _ in range(max_retries):
-        b = pack(n, items, want_layer_qubits, cap, lean)
+        b = pack(n, items, want_layer_qubits, cap, lean, extra_layers)
         if options is not None:
             backend.route(cfg, b, options)
         else:

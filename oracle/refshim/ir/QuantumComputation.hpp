@@ -151,10 +151,27 @@ public:
       if (!force && outputPermutation.count(physical) > 0) {
         continue;
       }
+      // as in mqt-core v3.1.0: the qubit's layout entries go, and when it
+      // came from the middle the logical indices above it move down by one
+      // (pinned by OPTIMAL_SOLUTIONS["4gt11_84"] in the reference's
+      // test_heuristic.cpp: gates on q[4] become logical qubit 3)
+      const auto logical = initialLayout.at(physical);
       initialLayout.erase(physical);
       outputPermutation.erase(physical);
       if (nqubits > 0) {
         --nqubits;
+      }
+      if (logical < nqubits + nancillae) {
+        for (auto& kv : initialLayout) {
+          if (kv.second > logical) {
+            --kv.second;
+          }
+        }
+        for (auto& kv : outputPermutation) {
+          if (kv.second > logical) {
+            --kv.second;
+          }
+        }
       }
     }
   }

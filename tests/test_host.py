@@ -1,0 +1,209 @@
+"""CPU suite: host-side logic of the product (no compute calls) - the C-ABI
+library loads and exports every symbol of include/qmap_b200.h, it refuses to
+compute without a CUDA device (no CPU fallback), the layering / splitting
+entry points, the OpenQASM-2 reader, the architecture / calibration parsers,
+and the sharding of instances over ranks (gloo, world size 2)."""
+import os
+import re
+import subprocess
+import sys
+import textwrap
+
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import parity
+from qmap_b200 import _abi, routing
+from qmap_b200 import architecture as ar
+from qmap_b200 import circuit as qcirc
+
+ROOT = parity.ROOT
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "qmap_b200.h")).read()
+    declared = set(re.findall(r"\b(qmg_[a-z0-9_]+)\s*\(", hdr))
+    # type names / macros that look like calls are not functions
+    declared = {d for d in declared if not d.endswith("_t")}
+    assert len(declared) >= 20
+    L = C.CDLL(_abi.LIB_PATH)
+    missing = [d for d in sorted(declared) if not hasattr(L, d)]
+    assert not missing, missing
+    assert set(_abi.EXPORTS) <= declared | {"qmg_config_default"}
+
+
+def test_no_cpu_fallback():
+    """Without a CUDA device every compute entry point returns QMG_NO_DEVICE."""
+    L = _abi.load()
+    if L.qmg_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    h = C.c_void_p()
+    e = np.array([[0, 1], [1, 0]], dtype=np.uint16)
+    rc = L.qmg_arch_create(2, e.ctypes.data, 2, 0, C.byref(h))
+    assert rc == _abi.QMG_NO_DEVICE
+    assert b"no CPU fallback" in L.qmg_last_error()
+    w = np.zeros((2, 2))
+    out = np.zeros((2, 2))
+    rc = L.qmg_build_table(2, e.ctypes.data, 2, w.ctypes.data, 0, out.ctypes.data, 0)
+    assert rc == _abi.QMG_NO_DEVICE
+    with pytest.raises(_abi.QmapError):
+        ar.Architecture(2, [(0, 1), (1, 0)]).handle
+
+
+def test_config_defaults_are_the_references():
+    """include/sc/configuration/Configuration.hpp:30-119"""
+    L = _abi.load()
+    c = _abi.QmgConfig()
+    L.qmg_config_default(C.byref(c))
+    py = routing.make_config()
+    for name, _ in _abi.QmgConfig._fields_:
+        assert getattr(c, name) == getattr(py, name), name
+    assert (c.heuristic, c.lookahead_heuristic, c.nr_lookaheads) == (0, 1, 15)
+    assert (c.first_lookahead_factor, c.lookahead_factor) == (0.75, 0.5)
+    assert (c.automatic_layer_splits, c.automatic_layer_splits_node_limit) == (1, 5000)
+    assert (c.layering, c.initial_layout) == (0, 2)
+
+
+def _layers_of(lc):
+    lay = lc.layers
+    nl = lay.n_layers
+    off2 = np.ctypeslib.as_array(C.cast(lay.gate2q_offsets, C.POINTER(C.c_uint32)), (nl + 1,))
+    g2 = np.ctypeslib.as_array(C.cast(lay.gates2q, C.POINTER(C.c_uint16)), (max(int(off2[-1]), 1), 4))
+    return nl, off2.copy(), g2[: off2[-1]].copy()
+
+
+def test_layering_individual_and_disjoint():
+    """Mapper::createLayers (src/sc/Mapper.cpp:138-281)"""
+    L = _abi.load()
+    # cx(0,1) h(2) cx(1,0) cx(2,3) cx(0,1)
+    c = np.array([0, -1, 1, 2, 0], dtype=np.int32)
+    t = np.array([1, 2, 0, 3, 1], dtype=np.int32)
+    ind = routing.LayeredCircuit(L, 4, c, t, 0)
+    assert ind.n_layers == 5
+    dq = routing.LayeredCircuit(L, 4, c, t, 1)
+    nl, off2, g2 = _layers_of(dq)
+    # disjoint qubits: {cx01, h2}, {cx10, cx23}, {cx01}
+    assert nl == 3
+    assert list(off2) == [0, 1, 3, 4]
+    assert g2[0].tolist() == [0, 1, 1, 0]
+    assert g2[1].tolist() == [0, 1, 0, 1] and g2[2].tolist() == [2, 3, 1, 0]
+    blk = routing.LayeredCircuit(L, 4, c, t, 4)
+    nl, off2, g2 = _layers_of(blk)
+    # disjoint 2q blocks: the three gates on (0,1) share one block with (2,3)
+    assert nl == 1
+    assert g2.tolist() == [[0, 1, 2, 1], [2, 3, 1, 0]]
+    assert blk.splittable(0) and not ind.splittable(0)
+    blk.split(0)
+    assert blk.n_layers == 2
+
+
+def test_router_rejects_unsuitable_settings():
+    """HeuristicMapper::checkParameters :149-167 (checkConfig in host_api.hpp,
+    called by every routing entry point before any work)"""
+    import emu_backend
+    n, e = parity.read_arch_file("ibm_qx4")
+    t = parity.golden_tables()
+    be = emu_backend.EmuBackend(n, e, t["ibm_qx4_dist"], t["ibm_qx4_dist_rev"])
+    c = np.array([0], dtype=np.int32)
+    tt = np.array([1], dtype=np.int32)
+    for kw in (dict(layering="odd_gates"), dict(layering="qubit_triangle"),
+               dict(heuristic="fidelity_best_location", lookahead_heuristic="none")):
+        cfg = routing.make_config(**kw)
+        item = routing.RouteItem(routing.LayeredCircuit(be.lib, n, c, tt, cfg.layering))
+        with pytest.raises(_abi.QmapError):
+            routing.route_batch(be, n, cfg, [item])
+
+
+def test_qasm_reader_and_mapper_view():
+    text = textwrap.dedent("""\
+        OPENQASM 2.0;
+        include "qelib1.inc";
+        qreg q[5];
+        creg c[5];
+        h q[0];
+        cx q[4],q[0];
+        rz(pi/4) q[2];
+        cx q[0], q[2];
+        measure q[0] -> c[0];
+        """)
+    circ = qcirc.parse_qasm(text)
+    assert circ.n_qubits == 5 and len(circ.ops) == 4 and circ.measurements == [(0, 0)]
+    assert circ.used_qubits() == [0, 2, 4]
+    c, t, ident = circ.mapper_view(5)
+    # idle qubits 1 and 3 are stripped: q2 -> logical 1, q4 -> logical 2;
+    # the identity layout keeps the original indices of the used qubits
+    assert c.tolist() == [-1, 2, -1, 0] and t.tolist() == [0, 0, 1, 1]
+    assert ident.tolist() == [0, -1, 2, -1, 4]
+    again = qcirc.parse_qasm(circ.to_qasm())
+    assert [o.qubits for o in again.ops] == [o.qubits for o in circ.ops]
+
+
+def test_arch_and_calibration_parsers_match_reference_costs():
+    """Architecture::loadCouplingMap / loadProperties / createFidelityTable
+    (src/sc/Architecture.cpp:57-81,108-166,232-294): the host-side -log2 costs
+    equal the reference's bit for bit (tests/golden/tables_golden.npz)."""
+    a = ar.Architecture().load_coupling_map(os.path.join(parity.ARCHS, "ibmq_london.arch"))
+    a.load_properties(os.path.join(parity.ARCHS, "ibmq_london.csv"))
+    t = parity.golden_tables()
+    c1, c2, cs = (a.single_qubit_fidelity_costs(), a.two_qubit_fidelity_costs(),
+                  a.swap_fidelity_costs())
+    assert np.array_equal(c1, t["ibmq_london_c1"])
+    assert np.array_equal(c2, t["ibmq_london_c2"])
+    assert np.array_equal(cs, t["ibmq_london_cswap"])
+    assert a.n_qubits == 5 and len(a.edges) == 8
+    assert a.to_arch_text().split()[0] == "5"
+
+
+def test_generated_architectures():
+    n, cm = ar.heavy_hex_27()
+    assert n == 27 and len(cm) == 56
+    n, cm = ar.heavy_hex_127()
+    assert n == 127 and len(cm) == 288
+    n, cm = ar.grid(32, 32)
+    assert n == 1024 and len(cm) == 3968
+
+
+def test_pack_and_unpack_roundtrip():
+    L = _abi.load()
+    c = np.array([0, 1], dtype=np.int32)
+    t = np.array([1, 2], dtype=np.int32)
+    lc = routing.LayeredCircuit(L, 3, c, t, 0)
+    b = routing.pack(3, [routing.RouteItem(lc, np.array([0, 1, 2], dtype=np.int16))], lean=True)
+    assert b.res[0].layers is None or not b.res[0].layers
+    assert b.res[0].layer_n_swaps
+    outs = routing.unpack(b)
+    assert outs[0].layers is None and len(outs[0].layer_n_swaps) == 2
+
+
+SHARD_SCRIPT = """
+import os, sys
+sys.path.insert(0, {root!r})
+import torch.distributed as dist
+import bench
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+seeds = list(bench.shard_seeds(rank, world, 10))
+got = [None] * world
+dist.all_gather_object(got, seeds)
+if rank == 0:
+    flat = [s for part in got for s in part]
+    assert sorted(flat) == list(range(10 * world)), flat
+    assert all(len(p) == 10 for p in got)
+    print("SHARDS_OK", flat[:3])
+dist.destroy_process_group()
+"""
+
+
+def test_instance_sharding_world_size_2(tmp_path):
+    """bench.py --gpus N: rank r routes seeds [r*B, (r+1)*B) - disjoint, equal
+    sized, no data-path collective (weak scaling)."""
+    script = tmp_path / "shard.py"
+    script.write_text(SHARD_SCRIPT.format(root=ROOT))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29631")
+    out = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+         "--master-addr", "127.0.0.1", "--master-port", "29631", str(script)],
+        capture_output=True, text=True, env=env, timeout=600)
+    assert "SHARDS_OK" in out.stdout, out.stdout + out.stderr
