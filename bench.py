@@ -210,10 +210,10 @@ def main():
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # before CUDA is initialised in this process (workers are spawned)
-        sample = args.cpu_sample or 2500 * cores
+        sample = args.cpu_sample or 6000 * cores
         exp, gen, swaps, busy, wall, search_s = run_reference(list(range(sample)), cores)
         cpu_base = {"value": exp / busy, "unit": "nodes/s", "cores": cores, "kind": "reference",
-                    "sample": f"first {sample} instances of the batch, {busy:.1f} s on {cores} processes",
+                    "sample": f"{sample} seeded instances of the workload (seeds 0..{sample - 1}), {busy:.1f} s on {cores} processes",
                     "circuits_per_s": sample / busy,
                     "search_loop_only_nodes_per_core_s": exp / search_s if search_s else None}
 

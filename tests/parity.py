@@ -114,23 +114,58 @@ def cuda_backend_for(ra, arch=None):
     return routing.CudaBackend(_abi.load(), arch.handle), arch
 
 
+def compare_outputs(a, b) -> str:
+    """Two routing.RouteOutput objects (e.g. CUDA vs the CPU restatement)."""
+    if a.status != b.status or a.n_layers_done != b.n_layers_done:
+        return f"status/layers {a.status}/{a.n_layers_done} != {b.status}/{b.n_layers_done}"
+    for l in range(a.n_layers_done):
+        for k in KEYS + ("n_swaps",):
+            if a.layers[l][k] != b.layers[l][k]:
+                return f"layer {l}: {k} {a.layers[l][k]} != {b.layers[l][k]}"
+        if not np.array_equal(a.layer_swaps(l), b.layer_swaps(l)):
+            return f"layer {l}: swaps differ"
+        if a.layer_qubits is not None and b.layer_qubits is not None and \
+                not np.array_equal(a.layer_qubits[l], b.layer_qubits[l]):
+            return f"layer {l}: layout differs"
+    if not np.array_equal(a.final_qubits, b.final_qubits):
+        return "final layout differs"
+    return ""
+
+
 def smoke_check() -> int:
-    """Used by __graft_entry__.smoke(): configs 1 and 2 on cuda:0 vs the oracle."""
+    """Used by __graft_entry__.smoke(): configs 1 and 2 on cuda:0 against the
+    oracle (the CPU restatement, itself pinned to the reference) and against
+    the committed outputs of the reference."""
+    from oracle import oracleapi
     from qmap_b200 import _abi
+    from qmap_b200.architecture import Architecture
     lib = _abi.load()
     total = 0
-    for arch_file, qasm, kw in (
-            ("ibm_qx4.arch", "4gt13_92.qasm", dict(lookahead_heuristic="none")),
-            ("ibm_qx5.arch", "qft_16.qasm", dict())):
-        ra = ref().arch_load(os.path.join(ARCHS, arch_file))
-        be, arch = cuda_backend_for(ra)
+    for arch_name, qasm, kw in (
+            ("ibm_qx4", "4gt13_92.qasm", dict(lookahead_heuristic="none")),
+            ("ibm_qx5", "qft_16.qasm", dict())):
+        n, edges = read_arch_file(arch_name)
+        arch = Architecture(n, [tuple(int(v) for v in e) for e in edges])
+        oa = oracleapi.OracleArch(n, edges)
         for inc in (False, True):
-            if not np.array_equal(arch.distance_table(inc), ra.distance_table(inc)):
-                raise AssertionError(f"{arch_file}: distance table differs from the oracle")
-        msg, out, rr = run_pair(be, lib, ra, os.path.join(CIRCUITS, qasm), **kw)
+            if not np.array_equal(arch.distance_table(inc), oa.distance_table(inc)):
+                raise AssertionError(f"{arch_name}: distance table differs from the oracle")
+        cfg = routing.make_config(debug=True, **kw)
+        circ = qcirc.load_qasm(os.path.join(CIRCUITS, qasm))
+        item = item_for(lib, n, circ, cfg)
+        out = routing.route_batch(routing.CudaBackend(lib, arch.handle), n, cfg, [item],
+                                  want_layer_qubits=True)[0]
+        want = routing.route_batch(oracleapi.OracleBackend(oa), n, cfg, [item],
+                                   want_layer_qubits=True)[0]
+        msg = compare_outputs(out, want)
         if msg:
-            raise AssertionError(f"{qasm} on {arch_file}: {msg}")
-        total += rr.n_layers
+            raise AssertionError(f"{qasm} on {arch_name} vs the oracle: {msg}")
+        g = next(g for g in golden_runs() if g.meta["arch"] == arch_name
+                 and g.meta["circuit"] == qasm and g.meta["config"] == kw)
+        msg = compare(out, g)
+        if msg:
+            raise AssertionError(f"{qasm} on {arch_name} vs the reference's output: {msg}")
+        total += out.n_layers_done
     return total
 
 

@@ -1,0 +1,136 @@
+"""-m gpu: the CUDA library (through the C ABI) against the committed outputs
+of the reference (tests/golden/route_golden.npz, tables_golden.npz) - these
+tests need no oracle library on the GPU box."""
+import os
+
+import numpy as np
+import pytest
+
+import parity
+from qmap_b200 import _abi, routing
+from qmap_b200 import architecture as ar
+from qmap_b200 import circuit as qcirc
+
+pytestmark = pytest.mark.gpu
+
+_archs = {}
+
+
+def arch_for(name, calib=None):
+    key = (name, calib)
+    if key not in _archs:
+        a = ar.Architecture().load_coupling_map(os.path.join(parity.ARCHS, name + ".arch"))
+        if calib:
+            a.load_properties(os.path.join(parity.ARCHS, calib))
+        _archs[key] = a
+    return _archs[key]
+
+
+def test_tables_match_reference_outputs():
+    t = parity.golden_tables()
+    names = sorted(k[:-5] for k in t.files if k.endswith("_dist"))
+    for name in names:
+        a = arch_for(name)
+        assert np.array_equal(a.distance_table(False), t[f"{name}_dist"]), name
+        assert np.array_equal(a.distance_table(True), t[f"{name}_dist_rev"]), name
+    a = arch_for("ibmq_london", "ibmq_london.csv")
+    assert np.array_equal(a.fidelity_distance_tables(), t["ibmq_london_fid"])
+
+
+RUNS = [g for g in parity.golden_runs() if not g.meta["split"]]
+
+
+@pytest.mark.parametrize("part", range(8))
+def test_route_matches_reference_outputs(part):
+    """every final-pass aStarMap call: costs, counters, result node id, layout,
+    SWAP list - bit-exact, fidelity costs included"""
+    assert len(RUNS) > 270
+    L = _abi.load()
+    bad = []
+    for g in RUNS[part::8]:
+        a = arch_for(g.meta["arch"], g.meta["calibration"])
+        be = routing.CudaBackend(L, a.handle)
+        kw = dict(g.meta["config"], debug=True)
+        cfg = routing.make_config(**kw)
+        circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
+        opts = None
+        if g.generated_nodes > 100000:
+            opts = _abi.QmgRouteOptions()
+            opts.pool_nodes = 1 << 20
+        out = routing.route_batch(be, a.n_qubits, cfg, [parity.item_for(L, a.n_qubits, circ, cfg)],
+                                  want_layer_qubits=True, options=opts)[0]
+        msg = parity.compare(out, g)
+        if msg:
+            bad.append((g.label, msg))
+    assert not bad, bad[:5]
+
+
+def test_batch_of_all_cases_per_configuration():
+    """many instances in ONE launch: all golden cases that share an architecture
+    and a configuration are routed as one batch (lean outputs) and every
+    instance's SWAP list / final layout / counters are checked"""
+    L = _abi.load()
+    groups = {}
+    for g in RUNS:
+        if g.generated_nodes > 100000:
+            continue
+        key = (g.meta["arch"], g.meta["calibration"], tuple(sorted(g.meta["config"].items())))
+        groups.setdefault(key, []).append(g)
+    checked = 0
+    for (arch, calib, kw), gs in groups.items():
+        a = arch_for(arch, calib)
+        cfg = routing.make_config(**dict(kw))
+        items = []
+        for g in gs:
+            circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
+            items.append(parity.item_for(L, a.n_qubits, circ, cfg))
+        # the same instances several times over, so that warps take >1 instance
+        reps = 3
+        outs = routing.route_batch(routing.CudaBackend(L, a.handle), a.n_qubits, cfg,
+                                   items * reps, lean=True)
+        for i, o in enumerate(outs):
+            g = gs[i % len(gs)]
+            assert o.status == 0, g.label
+            assert o.layers is None
+            assert np.array_equal(o.layer_n_swaps, g.calls["n_swaps"]), g.label
+            assert np.array_equal(o.swaps, g.swap_pairs), g.label
+            if g.n_layers:
+                assert np.array_equal(o.final_qubits, g.qubits_after[-1]), g.label
+            checked += 1
+    assert checked > 600
+
+
+def test_swap_buffer_too_small_is_reported_and_retried():
+    L = _abi.load()
+    g = next(g for g in RUNS if g.meta["circuit"] == "qft_16.qasm" and g.meta["arch"] == "ibm_qx5"
+             and not g.meta["config"])
+    a = arch_for("ibm_qx5")
+    cfg = routing.make_config()
+    circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, "qft_16.qasm"))
+    item = parity.item_for(L, a.n_qubits, circ, cfg)
+    be = routing.CudaBackend(L, a.handle)
+    b = routing.pack(a.n_qubits, [item], swap_capacity=8, lean=True)
+    be.route(cfg, b)
+    out = routing.unpack(b)[0]
+    assert out.status == _abi.QMG_BUFFER_TOO_SMALL
+    assert int(b.res[0].n_swaps_total) > 8  # the search stopped where the buffer overflowed
+    full = routing.route_batch(be, a.n_qubits, cfg, [item], lean=True)[0]
+    assert full.status == 0 and len(full.swaps) == g.swaps
+
+
+def test_workspace_is_reused_between_batches():
+    """the second call on one Architecture reuses the staging buffers and gives
+    identical results; a bigger batch afterwards grows them"""
+    L = _abi.load()
+    a = arch_for("ibm_qx5")
+    cfg = routing.make_config(initial_layout="identity")
+    circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, "qft_16.qasm"))
+    item = parity.item_for(L, a.n_qubits, circ, cfg)
+    be = routing.CudaBackend(L, a.handle)
+    first = routing.route_batch(be, a.n_qubits, cfg, [item] * 8, lean=True)
+    second = routing.route_batch(be, a.n_qubits, cfg, [item] * 8, lean=True)
+    big = routing.route_batch(be, a.n_qubits, cfg, [item] * 700, lean=True)
+    for o in second + big:
+        assert o.status == 0
+        assert np.array_equal(o.swaps, first[0].swaps)
+        assert o.expanded_nodes == first[0].expanded_nodes
