@@ -242,7 +242,10 @@ def main():
         items.append(routing.RouteItem(lc, np.arange(n, dtype=np.int16)))
     opts = _abi.QmgRouteOptions()
     opts.searches_per_sm = args.searches_per_sm
-    bufs = routing.pack(n, items)
+    # what routeCircuit consumes: per-layer SWAP lists + layouts (the per-call
+    # benchmark records of config.debug are not requested)
+    opts.lean_outputs = 1
+    bufs = routing.pack(n, items, lean=True)
     batch = C.c_void_p()
     _abi.check(L, L.qmg_batch_create(h, C.byref(cfg), len(items), C.addressof(bufs.inst),
                                      C.byref(opts), C.byref(batch)))

@@ -317,7 +317,10 @@ typedef struct {
   uint32_t pool_nodes;       /* node-pool capacity per resident search, 0=auto */
   uint32_t threads_per_search; /* 32..256, 0 = auto from n */
   uint32_t searches_per_sm;  /* resident searches per SM, 0 = auto */
-  uint32_t _pad;
+  /* qmg_batch_create only: keep the compact per-layer outputs (SWAP counts,
+   * SWAP lists, layouts) instead of the full qmg_layer_result records; with
+   * qmg_route_batch the result pointers decide */
+  uint32_t lean_outputs;
 } qmg_route_options;
 
 typedef struct {

@@ -32,7 +32,7 @@ struct qmg_batch {
   size_t iInst = 0, iOrder = 0, iMem = 0, iTicket = 0, inSize = 0;
   size_t tableOff = 0, tableBytes = 0;
   uint32_t grid = 0, poolNodes = 0;
-  SmemLayout sl{};
+  Scratch sl{};
   size_t smemBytes = 0;
   uint64_t h2dBytes = 0;
   float h2dMs = 0.F;
@@ -216,7 +216,8 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     b->totSwapCap += cap;
   }
   if (capacities == nullptr) {
-    b->wantLayers = true;  // device-resident batches keep the full records
+    // device-resident batches keep the full records unless told otherwise
+    b->wantLayers = opt == nullptr || opt->lean_outputs == 0;
   }
   if (b->totLayers > 0xFFFFFFF0ULL || b->totSwapCap > 0x3FFFFFF0ULL) {
     return fail(QMG_BAD_ARG, "batch too large");
@@ -228,8 +229,12 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   sc.mark("sizes");
   // ---- launch geometry
   const DeviceLimits& prop = arch->limits;
-  b->sl = smemLayout(n);
-  b->smemBytes = static_cast<size_t>(b->sl.bytesPerWarp) * kWarpsPerCta;
+  b->sl = scratchLayout(n);
+  if (b->sl.bytes > kMaxScratchBytes) {
+    return fail(QMG_BAD_ARG, "architecture too large for the shared-memory "
+                             "working set of one search");
+  }
+  b->smemBytes = static_cast<size_t>(b->sl.bytes) * kWarpsPerCta;
   if (b->smemBytes > prop.sharedMemPerBlockOptin) {
     return fail(QMG_BAD_ARG, "architecture too large for the shared-memory "
                              "working set of one search");

@@ -18,52 +18,33 @@ constexpr int kWarpsPerCta = 4;
 #define QMG_MIN_CTAS 8
 #endif
 
-struct SmemLayout {
-  uint32_t bytesPerWarp;
-  uint32_t offL, offCurQ, offCurL, offMask, offCh, offLookPen;
-};
-
-inline SmemLayout smemLayout(int n) {
-  auto al = [](uint32_t v) { return (v + 15U) & ~15U; };
-  SmemLayout s{};
-  uint32_t o = 0;
-  o += al(static_cast<uint32_t>(n) * 2U);  // Q
-  s.offL = o;
-  o += al(static_cast<uint32_t>(n) * 2U);
-  s.offCurQ = o;
-  o += al(static_cast<uint32_t>(n) * 2U);
-  s.offCurL = o;
-  o += al(static_cast<uint32_t>(n) * 2U);
-  s.offMask = o;
-  o += al((static_cast<uint32_t>(n) + 31U) / 32U * 4U + 4U);
-  s.offCh = o;
-  o += al(static_cast<uint32_t>(sizeof(Child)) * kChunk);
-  s.offLookPen = o;
-  o += al(8U * (kChunk / 2) * kLookBlock);
-  s.bytesPerWarp = o;
-  return s;
-}
+// upper bound of the per-warp working set (4 warps of a CTA must fit the
+// 227 KB of shared memory a CTA can opt into)
+constexpr uint32_t kMaxScratchBytes = 56000;
 
 template <int H>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
     route_kernel(ArchView A, CfgView C, const InstView* __restrict__ inst,
                  const uint32_t* __restrict__ order, uint32_t nInst,
                  SearchMem* __restrict__ mem, uint32_t* __restrict__ ticket,
-                 SmemLayout sl) {
+                 Scratch lay) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = static_cast<int>(threadIdx.x) >> 5;
   const int lane = static_cast<int>(threadIdx.x) & 31;
   const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
-  uint8_t* base = smem + static_cast<size_t>(warp) * sl.bytesPerWarp;
-  Scratch S;
-  S.Q = reinterpret_cast<int16_t*>(base);
-  S.L = reinterpret_cast<int16_t*>(base + sl.offL);
-  S.curQ = reinterpret_cast<int16_t*>(base + sl.offCurQ);
-  S.curL = reinterpret_cast<int16_t*>(base + sl.offCurL);
-  S.consMask = reinterpret_cast<uint32_t*>(base + sl.offMask);
-  S.ch = reinterpret_cast<Child*>(base + sl.offCh);
-  S.lookPen = reinterpret_cast<double*>(base + sl.offLookPen);
-  SearchMem M = mem[gw];
+  Scratch S = lay;
+  S.base = smem + static_cast<size_t>(warp) * lay.bytes;
+  // the warp-uniform descriptors are kept in shared memory, not in registers
+  InstView* sI = S.inst();
+  SearchMem* sM = S.mem();
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(mem + gw);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(sM);
+    for (uint32_t w = lane; w < sizeof(SearchMem) / 4; w += 32) {
+      dst[w] = src[w];
+    }
+  }
+  __syncwarp();
   for (;;) {
     uint32_t t = 0;
     if (lane == 0) {
@@ -73,13 +54,30 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
     if (t >= nInst) {
       break;
     }
-    const InstView I = inst[order[t]];
-    Search<H> s(A, C, I, M, S);
+    {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(inst + order[t]);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(sI);
+      for (uint32_t w = lane; w < sizeof(InstView) / 4; w += 32) {
+        dst[w] = __ldg(src + w);
+      }
+    }
+    __syncwarp();
+#ifdef QMG_DESC_REGS
+    const InstView rI = *sI;
+    SearchMem rM = *sM;
+    Search<H> s(A, C, rI, rM, S);
     s.run();
+    if (lane == 0) {
+      sM->stamp = rM.stamp;
+    }
+#else
+    Search<H> s(A, C, *sI, *sM, S);
+    s.run();
+#endif
     __syncwarp();
   }
   if (lane == 0) {
-    mem[gw].stamp = M.stamp;
+    mem[gw].stamp = sM->stamp;
   }
 }
 

@@ -39,6 +39,8 @@ constexpr double kTol = 1e-6;          // HeuristicMapper.hpp:463,473
 constexpr uint32_t kNone = 0xFFFFFFFFU;
 constexpr int kChunk = 32;    // children scored per pass
 constexpr int kLookBlock = 16; // lookahead layers scored per pass
+// lookahead scratch: a (kChunk/2) x kLookBlock block of terms
+constexpr int kLookPenDoubles = (kChunk / 2) * kLookBlock;
 constexpr uint32_t kScanMax = 96;  // open-list length up to which push() scans
 
 enum Status : int32_t {
@@ -179,16 +181,61 @@ struct SearchMem {
   uint32_t maxG;
 };
 
-// per resident search, in shared memory (device) / plain arrays (host)
+// per resident search, in shared memory (device) / one byte buffer (host).
+// Fixed-size sections come first so that their offsets are compile-time
+// constants (immediates of the shared-memory instructions); the
+// n-dependent sections follow at multiples of one stride:
+// [ch][lookPen][InstView][SearchMem] [Q][L][curQ][curL][consMask]
+constexpr uint32_t kAl16(uint32_t v) { return (v + 15U) & ~15U; }
+constexpr uint32_t kOffCh = 0;
+constexpr uint32_t kOffLook = kOffCh + kAl16(sizeof(Child) * kChunk);
+constexpr uint32_t kOffInst = kOffLook + kAl16(8U * kLookPenDoubles);
+constexpr uint32_t kOffMem = kOffInst + kAl16(sizeof(InstView));
+constexpr uint32_t kOffVar = kOffMem + kAl16(sizeof(SearchMem));
 struct Scratch {
-  int16_t* Q;     // layout of the node being expanded
-  int16_t* L;
-  int16_t* curQ;  // Mapper::qubits / Mapper::locations of the instance
-  int16_t* curL;
-  uint32_t* consMask;
-  Child* ch;
-  double* lookPen;       // (kChunk / 2) * kLookBlock; also output staging
-  };
+  uint8_t* base;
+  uint32_t stride;  // bytes of one n-entry int16 section (16-byte aligned)
+  uint32_t bytes;
+  QMG_HD Child* ch() const { return reinterpret_cast<Child*>(base + kOffCh); }
+  // kLookPenDoubles doubles; also output staging
+  QMG_HD double* lookPen() const {
+    return reinterpret_cast<double*>(base + kOffLook);
+  }
+  QMG_HD InstView* inst() const {
+    return reinterpret_cast<InstView*>(base + kOffInst);
+  }
+  QMG_HD SearchMem* mem() const {
+    return reinterpret_cast<SearchMem*>(base + kOffMem);
+  }
+  // layout of the node being expanded
+  QMG_HD int16_t* Q() const {
+    return reinterpret_cast<int16_t*>(base + kOffVar);
+  }
+  QMG_HD int16_t* L() const {
+    return reinterpret_cast<int16_t*>(base + kOffVar + stride);
+  }
+  // Mapper::qubits / Mapper::locations of the instance
+  QMG_HD int16_t* curQ() const {
+    return reinterpret_cast<int16_t*>(base + kOffVar + 2 * stride);
+  }
+  QMG_HD int16_t* curL() const {
+    return reinterpret_cast<int16_t*>(base + kOffVar + 3 * stride);
+  }
+  QMG_HD uint32_t* consMask() const {
+    return reinterpret_cast<uint32_t*>(base + kOffVar + 4 * stride);
+  }
+};
+
+// section sizes for an n-qubit architecture; base is set by the owner of the
+// buffer
+inline Scratch scratchLayout(int n) {
+  Scratch s{};
+  s.base = nullptr;
+  s.stride = kAl16(static_cast<uint32_t>(n) * 2U + 2U);
+  s.bytes = kOffVar + 4 * s.stride +
+            kAl16((static_cast<uint32_t>(n) + 31U) / 32U * 4U + 4U);
+  return s;
+}
 
 QMG_HD uint32_t mix32(uint32_t x) {
   x ^= x >> 16;
@@ -394,11 +441,11 @@ template <int H> struct Search {
   }
   QMG_HD int16_t* nodeL(uint32_t idx) const { return nodeQ(idx) + n; }
   QMG_HD bool considered(int q) const {
-    return (S.consMask[q >> 5] >> (q & 31)) & 1U;
+    return (S.consMask()[q >> 5] >> (q & 31)) & 1U;
   }
 
   // ------------------------------------------------------------------------
-  // scoring of one node: the parent layout (S.Q / S.L) with the SWAP on the
+  // scoring of one node: the parent layout (S.Q() / S.L()) with the SWAP on the
   // physical edge (a, b) applied; a == b scores the layout itself (root).
   // Executed by ONE lane (gate-count heuristics).
   // ------------------------------------------------------------------------
@@ -617,6 +664,48 @@ template <int H> struct Search {
     out.heur = heur;
   }
 
+  // the contribution of ONE gate of a later layer to the lookahead penalty
+  // (:1387-1513) under the layout "parent with swap (a,b)" (a < 0: the parent
+  // itself).  Returns false when both operands are unplaced (no penalty).
+  QMG_HD bool lookaheadGateCost(const Gate2& e, int a, int b, int q1, int q2,
+                                double& cost) const {
+    const int loc1 = locAfter(e.q1, q1, q2, a, b);
+    const int loc2 = locAfter(e.q2, q1, q2, a, b);
+    if (loc1 < 0 && loc2 < 0) {
+      return false;
+    }
+    if (loc1 < 0 || loc2 < 0) {
+      // the placed partner; the other one may go to any free qubit
+      const bool firstFree = loc1 < 0;
+      const int loc = firstFree ? loc2 : loc1;
+      double mn = DBL_MAX;
+      QMG_NOUNROLL
+      for (int j = 0; j < n; ++j) {
+        const int qj = (j == a) ? q2 : ((j == b) ? q1 : pQ[j]);
+        if (qj != -1) {
+          continue;
+        }
+        // :1405-1412 (loc1 free) and :1421-1428 (loc2 free)
+        if (e.fwd > 0) {
+          mn = fmin(mn, firstFree ? dRev(j, loc) : dRev(loc, j));
+        }
+        if (e.rev > 0) {
+          mn = fmin(mn, firstFree ? dRev(loc, j) : dRev(j, loc));
+        }
+      }
+      cost = mn;
+    } else {
+      cost = DBL_MAX;
+      if (e.fwd > 0) {
+        cost = fmin(cost, dRev(loc1, loc2));
+      }
+      if (e.rev > 0) {
+        cost = fmin(cost, dRev(loc2, loc1));
+      }
+    }
+    return true;
+  }
+
   // lookaheadGateCountMaxDistance / SumDistance :1387-1513 for one later
   // layer and one child layout.  Executed by ONE lane.
   QMG_HD double lookaheadPenalty(uint32_t ll, int a, int b, int q1,
@@ -628,40 +717,9 @@ template <int H> struct Search {
     QMG_NOUNROLL
     for (uint32_t i = lo; i < hi; ++i) {
       const Gate2 e = ldGate(I.circ.g2 + i);
-      const int loc1 = locAfter(e.q1, q1, q2, a, b);
-      const int loc2 = locAfter(e.q2, q1, q2, a, b);
       double cost;
-      if (loc1 < 0 && loc2 < 0) {
+      if (!lookaheadGateCost(e, a, b, q1, q2, cost)) {
         continue;
-      }
-      if (loc1 < 0 || loc2 < 0) {
-        // the placed partner; the other one may go to any free qubit
-        const bool firstFree = loc1 < 0;
-        const int loc = firstFree ? loc2 : loc1;
-        double mn = DBL_MAX;
-        QMG_NOUNROLL
-        for (int j = 0; j < n; ++j) {
-          const int qj = (j == a) ? q2 : ((j == b) ? q1 : pQ[j]);
-          if (qj != -1) {
-            continue;
-          }
-          // :1405-1412 (loc1 free) and :1421-1428 (loc2 free)
-          if (e.fwd > 0) {
-            mn = fmin(mn, firstFree ? dRev(j, loc) : dRev(loc, j));
-          }
-          if (e.rev > 0) {
-            mn = fmin(mn, firstFree ? dRev(loc, j) : dRev(j, loc));
-          }
-        }
-        cost = mn;
-      } else {
-        cost = DBL_MAX;
-        if (e.fwd > 0) {
-          cost = fmin(cost, dRev(loc1, loc2));
-        }
-        if (e.rev > 0) {
-          cost = fmin(cost, dRev(loc2, loc1));
-        }
       }
       if (isMax) {
         penalty = fmax(penalty, cost);
@@ -672,7 +730,7 @@ template <int H> struct Search {
     return penalty;
   }
 
-  // updateLookaheadPenalty :1356-1385 for the cnt children in S.ch (or the
+  // updateLookaheadPenalty :1356-1385 for the cnt children in S.ch() (or the
   // root when rootOnly).  Items (child, lookahead layer) are spread over the
   // lanes (16 lookahead layers x 16 children per pass); the factor-weighted
   // sum is then accumulated per child in layer order with the reference's
@@ -681,7 +739,7 @@ template <int H> struct Search {
     if (C.lookahead == 0 || nLook == 0) {
       QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
-        S.ch[c].look = 0.;
+        S.ch()[c].look = 0.;
       }
       g.sync();
       return;
@@ -692,7 +750,7 @@ template <int H> struct Search {
       const int nc = (cnt - c0) < kHalf ? (cnt - c0) : kHalf;
       QMG_NOUNROLL
       for (int c = g.lane; c < nc; c += Group::W) {
-        S.ch[c0 + c].look = 0.;
+        S.ch()[c0 + c].look = 0.;
       }
       QMG_NOUNROLL
       for (uint32_t s0 = 0; s0 < nLook; s0 += kLookBlock) {
@@ -710,24 +768,27 @@ template <int H> struct Search {
           }
           int a = -1, b = -1, q1 = -2, q2 = -2;
           if (!rootOnly) {
-            const Child& ch = S.ch[c0 + c];
+            const Child& ch = S.ch()[c0 + c];
             a = ch.a;
             b = ch.b;
             q1 = pQ[a];
             q2 = pQ[b];
           }
-          S.lookPen[it] =
+          // factor_i * penalty_i (rounded as in the reference, then summed
+          // in layer order below)
+          S.lookPen()[it] =
+              ldg(C.factors + s0 + sl) *
               lookaheadPenalty(ldg(lookLayers + s0 + sl), a, b, q1, q2);
         }
         g.sync();
         QMG_NOUNROLL
         for (int c = g.lane; c < nc; c += Group::W) {
-          double acc = S.ch[c0 + c].look;
+          double acc = S.ch()[c0 + c].look;
           QMG_NOUNROLL
           for (uint32_t sl = 0; sl < nb; ++sl) {
-            acc += ldg(C.factors + s0 + sl) * S.lookPen[c * kLookBlock + sl];
+            acc += S.lookPen()[c * kLookBlock + sl];
           }
-          S.ch[c0 + c].look = acc;
+          S.ch()[c0 + c].look = acc;
         }
       }
     }
@@ -1191,7 +1252,7 @@ template <int H> struct Search {
     return true;
   }
 
-  // score the cnt nodes in S.ch (their a/b are set; root: the layout itself):
+  // score the cnt nodes in S.ch() (their a/b are set; root: the layout itself):
   // costs, layout hash and lookahead penalty
   QMG_HD void evaluate(int cnt, bool root, const ParentCosts& pc,
                        uint64_t parentHash) {
@@ -1200,34 +1261,34 @@ template <int H> struct Search {
       QMG_NOUNROLL
       for (int c = 0; c < cnt; ++c) {
         Child out;
-        scoreFidelity(root ? 0 : S.ch[c].a, root ? 0 : S.ch[c].b, pc, out);
+        scoreFidelity(root ? 0 : S.ch()[c].a, root ? 0 : S.ch()[c].b, pc, out);
         if (g.lane == 0) {
-          S.ch[c].fixed = out.fixed;
-          S.ch[c].rev = out.rev;
-          S.ch[c].heur = out.heur;
-          S.ch[c].shared = 0;
-          S.ch[c].nValid = out.nValid;
-          S.ch[c].valid = out.valid;
+          S.ch()[c].fixed = out.fixed;
+          S.ch()[c].rev = out.rev;
+          S.ch()[c].heur = out.heur;
+          S.ch()[c].shared = 0;
+          S.ch()[c].nValid = out.nValid;
+          S.ch()[c].valid = out.valid;
         }
       }
     } else {
       QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
         Child out;
-        const int a = root ? 0 : S.ch[c].a;
-        const int b = root ? 0 : S.ch[c].b;
+        const int a = root ? 0 : S.ch()[c].a;
+        const int b = root ? 0 : S.ch()[c].b;
         scoreGateCount(a, b, pc, out,
                        M.nsw + static_cast<size_t>(g.lane) * M.maxG);
-        S.ch[c].fixed = out.fixed;
-        S.ch[c].rev = out.rev;
-        S.ch[c].heur = out.heur;
-        S.ch[c].shared = out.shared;
-        S.ch[c].nValid = out.nValid;
-        S.ch[c].valid = out.valid;
+        S.ch()[c].fixed = out.fixed;
+        S.ch()[c].rev = out.rev;
+        S.ch()[c].heur = out.heur;
+        S.ch()[c].shared = out.shared;
+        S.ch()[c].nValid = out.nValid;
+        S.ch()[c].valid = out.valid;
         if (!root) {
           const int q1 = pQ[a];
           const int q2 = pQ[b];
-          S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
+          S.ch()[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
                          cellHash(a, q2) + cellHash(b, q1);
         }
       }
@@ -1235,16 +1296,15 @@ template <int H> struct Search {
     if (kFid && !root) {
       QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
-        const int a = S.ch[c].a;
-        const int b = S.ch[c].b;
+        const int a = S.ch()[c].a;
+        const int b = S.ch()[c].b;
         const int q1 = pQ[a];
         const int q2 = pQ[b];
-        S.ch[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
+        S.ch()[c].hash = parentHash - cellHash(a, q1) - cellHash(b, q2) +
                        cellHash(a, q2) + cellHash(b, q1);
       }
     }
     g.sync();
-    scoreLookahead(cnt, root);
   }
 
   // expandNode :698-727, resumable.  The candidate order (considered qubit
@@ -1252,7 +1312,7 @@ template <int H> struct Search {
   // reproduced by a closed form: a swap between two occupied physical qubits
   // is generated only from the smallest considered qubit of the pair and only
   // on the smaller of the (up to two) directed edges between them.  Fills
-  // S.ch[0..cnt) with up to kChunk swaps and sets enumDone when the parent is
+  // S.ch()[0..cnt) with up to kChunk swaps and sets enumDone when the parent is
   // exhausted.
   uint32_t enumCi = 0, enumK = 0;
   bool enumDone = true;
@@ -1294,8 +1354,8 @@ template <int H> struct Search {
         }
         if (keep) {
           const int rank = popc32(bal & ((1U << g.lane) - 1U));
-          S.ch[cnt + rank].a = static_cast<uint16_t>(ea);
-          S.ch[cnt + rank].b = static_cast<uint16_t>(eb);
+          S.ch()[cnt + rank].a = static_cast<uint16_t>(ea);
+          S.ch()[cnt + rank].b = static_cast<uint16_t>(eb);
         }
         cnt += add;
         enumK += Group::W;
@@ -1309,15 +1369,15 @@ template <int H> struct Search {
 
 
   // ------------------------------------------------------------------------
-  // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on S.curQ / S.curL
+  // mapUnmappedGates :211-285 / mapToMinDistance :287-307 on S.curQ() / S.curL()
   // ------------------------------------------------------------------------
   uint32_t nPlace = 0;  // running count into I.places
   bool record = false;
 
   QMG_HD void place(int logical, int phys) {
     if (g.lane == 0) {
-      S.curQ[phys] = static_cast<int16_t>(logical);
-      S.curL[logical] = static_cast<int16_t>(phys);
+      S.curQ()[phys] = static_cast<int16_t>(logical);
+      S.curL()[logical] = static_cast<int16_t>(phys);
       if (record && I.places != nullptr && nPlace < I.placeCap) {
         I.places[2 * nPlace] = static_cast<uint16_t>(logical);
         I.places[2 * nPlace + 1] = static_cast<uint16_t>(phys);
@@ -1333,7 +1393,7 @@ template <int H> struct Search {
     QMG_NOUNROLL
     for (int p0 = 0; p0 < n; p0 += Group::W) {
       const int p = p0 + g.lane;
-      const uint32_t bal = g.ballot(p < n && S.curQ[p] == -1);
+      const uint32_t bal = g.ballot(p < n && S.curQ()[p] == -1);
       if (bal != 0) {
         return p0 + ctz32(bal);
       }
@@ -1342,12 +1402,12 @@ template <int H> struct Search {
   }
 
   QMG_HD bool mapToMinDistance(int source, int target) {
-    const int src = S.curL[source];
+    const int src = S.curL()[source];
     double best = DBL_MAX;
     uint32_t pos = kNone;
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
-      if (S.curQ[i] == -1) {
+      if (S.curQ()[i] == -1) {
         const double d = dRev(src, i);
         if (d < best) {
           best = d;
@@ -1369,7 +1429,7 @@ template <int H> struct Search {
       QMG_NOUNROLL
       for (uint32_t i = 0; i < G1; ++i) {
         const Gate1 e = ldGate1(gates1 + i);
-        if (S.curL[e.q] == -1) {
+        if (S.curL()[e.q] == -1) {
           const int p = firstFree();
           if (p >= 0) {
             place(e.q, p);
@@ -1380,8 +1440,8 @@ template <int H> struct Search {
     QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
-      const int l1 = S.curL[e.q1];
-      const int l2 = S.curL[e.q2];
+      const int l1 = S.curL()[e.q1];
+      const int l2 = S.curL()[e.q2];
       if (l1 == -1 && l2 == -1) {
         // first coupling edge (ascending) with both ends free
         int ca = -1;
@@ -1391,8 +1451,8 @@ template <int H> struct Search {
           const int k = k0 + g.lane;
           bool ok = false;
           if (k < A.nE) {
-            ok = S.curQ[ldg(A.edges + 2 * k)] == -1 &&
-                 S.curQ[ldg(A.edges + 2 * k + 1)] == -1;
+            ok = S.curQ()[ldg(A.edges + 2 * k)] == -1 &&
+                 S.curQ()[ldg(A.edges + 2 * k + 1)] == -1;
           }
           const uint32_t bal = g.ballot(ok);
           if (bal != 0) {
@@ -1409,12 +1469,12 @@ template <int H> struct Search {
           uint32_t code = kNone;
           QMG_NOUNROLL
           for (int i = g.lane; i < n; i += Group::W) {
-            if (S.curQ[i] != -1) {
+            if (S.curQ()[i] != -1) {
               continue;
             }
             QMG_NOUNROLL
             for (int j = i + 1; j < n; ++j) {
-              if (S.curQ[j] != -1) {
+              if (S.curQ()[j] != -1) {
                 continue;
               }
               const double d = dRev(i, j);
@@ -1483,14 +1543,14 @@ template <int H> struct Search {
     g.sync();
     QMG_NOUNROLL
     for (int w = g.lane; w < (n + 31) / 32; w += Group::W) {
-      S.consMask[w] = 0;
+      S.consMask()[w] = 0;
     }
     g.sync();
     if (g.lane == 0) {
       QMG_NOUNROLL
       for (uint32_t i = 0; i < nCons; ++i) {
         const int q = ldg(cons + i);
-        S.consMask[q >> 5] |= 1U << (q & 31);
+        S.consMask()[q >> 5] |= 1U << (q & 31);
       }
     }
     maskReady = true;
@@ -1502,7 +1562,11 @@ template <int H> struct Search {
     nOpen = 0;
     nextId = 0;
     tableMode = false;
-    ++M.stamp;
+    g.sync();
+    if (g.lane == 0) {
+      ++M.stamp;  // (M lives in shared memory on the device)
+    }
+    g.sync();
     const bool splittable =
         C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
     // one loop iteration = evaluate one chunk of nodes (first the root from
@@ -1519,16 +1583,26 @@ template <int H> struct Search {
     ParentCosts pc;
     pc.fixed = 0.;
     pc.shared = 0;
-    pQ = S.curQ;
-    pL = S.curL;
+    pQ = S.curQ();
+    pL = S.curL();
     enumDone = true;
+    // the root's lookahead penalty is only reported, never compared, when the
+    // root is a goal of a tight heuristic
+    const bool rootLookWanted = record && I.layers != nullptr;
     QMG_NOUNROLL
     for (;;) {
       const int cnt = rootMode ? 1 : gatherChunk();
       if (cnt > 0) {
         evaluate(cnt, rootMode, pc, parentHash);
+        bool goalRoot = false;
         if (rootMode) {
-          if (S.ch[0].valid != 0 && kTight) {
+          goalRoot = S.ch()[0].valid != 0 && kTight;
+        }
+        if (!goalRoot || rootLookWanted) {
+          scoreLookahead(cnt, rootMode);
+        }
+        if (rootMode) {
+          if (goalRoot) {
             // the root is a goal and the heuristic is tight: the first pop
             // ends the search (:585-599) - no node record is needed
             nextId = 1;
@@ -1543,15 +1617,15 @@ template <int H> struct Search {
           }
           hsh = gsum64(g, hsh);
           if (g.lane == 0) {
-            S.ch[0].hash = hsh;
-            S.ch[0].a = 0;
-            S.ch[0].b = 0;
+            S.ch()[0].hash = hsh;
+            S.ch()[0].a = 0;
+            S.ch()[0].b = 0;
           }
           g.sync();
         }
         QMG_NOUNROLL
         for (int c = 0; c < cnt; ++c) {
-          const Child ch = S.ch[c];
+          const Child ch = S.ch()[c];
           if (!push(ch, parent, depth, rootMode)) {
             return ST_POOL;
           }
@@ -1629,8 +1703,8 @@ template <int H> struct Search {
       if (!maskReady) {
         buildMask();
       }
-      pQ = S.Q;
-      pL = S.L;
+      pQ = S.Q();
+      pL = S.L();
       const int16_t* nq = nodeQ(cur);
       const int16_t* nl = nodeL(cur);
       QMG_NOUNROLL
@@ -1657,6 +1731,26 @@ template <int H> struct Search {
 
   // one aStarMap call incl. mapUnmappedGates; adopts the result layout
   QMG_HD int routeLayer(uint32_t l, bool finalPass, uint32_t& swapTotal) {
+    const bool wantRec = finalPass && I.layers != nullptr;
+    if (!kFid && !wantRec) {
+      // a layer without 2q gates needs no search when no record of it is
+      // wanted: nothing to place, the root (1 generated node) is the result
+      if (ldg(I.circ.g2Off + l + 1) == ldg(I.circ.g2Off + l)) {
+        totGenerated += 1;
+        if (finalPass) {
+          if (I.layerNSwaps != nullptr && g.lane == 0) {
+            I.layerNSwaps[l] = 0;
+          }
+          if (I.layerQ != nullptr) {
+            QMG_NOUNROLL
+            for (int i = g.lane; i < n; i += Group::W) {
+              I.layerQ[static_cast<size_t>(l) * n + i] = S.curQ()[i];
+            }
+          }
+        }
+        return ST_OK;
+      }
+    }
     setLayer(l);
     const uint32_t placeBefore = nPlace;
     record = finalPass;
@@ -1673,11 +1767,11 @@ template <int H> struct Search {
     g.sync();
     // the 15 eight-byte fields of LayerOut are staged in shared memory and
     // written by 15 lanes as one coalesced 120-byte store
-    uint64_t* stage = reinterpret_cast<uint64_t*>(S.lookPen);
+    uint64_t* stage = reinterpret_cast<uint64_t*>(S.lookPen());
     uint32_t d = 0;
     if (st.rootResult) {
-      if (finalPass && g.lane == 0) {
-        const Child& r = S.ch[0];
+      if (wantRec && g.lane == 0) {
+        const Child& r = S.ch()[0];
         LayerOut o{};
         o.cost_fixed = r.fixed;
         o.cost_fixed_reversals = r.rev;
@@ -1691,7 +1785,7 @@ template <int H> struct Search {
       if (finalPass && I.layerQ != nullptr) {
         QMG_NOUNROLL
         for (int i = g.lane; i < n; i += Group::W) {
-          I.layerQ[static_cast<size_t>(l) * n + i] = S.curQ[i];
+          I.layerQ[static_cast<size_t>(l) * n + i] = S.curQ()[i];
         }
       }
     } else {
@@ -1703,13 +1797,13 @@ template <int H> struct Search {
       QMG_NOUNROLL
       for (int i = g.lane; i < n; i += Group::W) {
         const int16_t vq = rq[i];
-        S.curQ[i] = vq;
-        S.curL[i] = rl[i];
+        S.curQ()[i] = vq;
+        S.curL()[i] = rl[i];
         if (finalPass && I.layerQ != nullptr) {
           I.layerQ[static_cast<size_t>(l) * n + i] = vq;
         }
       }
-      if (finalPass && g.lane == 0) {
+      if (wantRec && g.lane == 0) {
         LayerOut o{};
         o.cost_fixed = h->fixed;
         o.cost_fixed_reversals = h->rev;
@@ -1719,6 +1813,8 @@ template <int H> struct Search {
         o.depth = d;
         o.resultId = h->id;
         *reinterpret_cast<LayerOut*>(stage) = o;
+      }
+      if (finalPass && g.lane == 0) {
         // swaps root -> result
         if (I.swaps != nullptr && swapTotal + d <= I.swapCap) {
           uint32_t cur = res;
@@ -1777,17 +1873,17 @@ template <int H> struct Search {
     const uint32_t nL = I.circ.nLayers;
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
-      S.curQ[i] = -1;
-      S.curL[i] = -1;
+      S.curQ()[i] = -1;
+      S.curL()[i] = -1;
     }
     g.sync();
     if (I.initLoc != nullptr) {
       QMG_NOUNROLL
       for (int i = g.lane; i < n; i += Group::W) {
         const int16_t p = I.initLoc[i];
-        S.curL[i] = p;
+        S.curL()[i] = p;
         if (p >= 0) {
-          S.curQ[p] = static_cast<int16_t>(i);
+          S.curQ()[p] = static_cast<int16_t>(i);
         }
       }
     }
@@ -1810,7 +1906,7 @@ template <int H> struct Search {
       if (I.startL != nullptr) {
         QMG_NOUNROLL
         for (int i = g.lane; i < n; i += Group::W) {
-          I.startL[i] = S.curL[i];
+          I.startL[i] = S.curL()[i];
         }
       }
       const uint32_t first = I.firstLayer;
@@ -1829,8 +1925,8 @@ template <int H> struct Search {
     g.sync();
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
-      I.finalQ[i] = S.curQ[i];
-      I.finalL[i] = S.curL[i];
+      I.finalQ[i] = S.curQ()[i];
+      I.finalL[i] = S.curL()[i];
     }
     uint32_t packedOff = 0;
     if (I.swapsPacked != nullptr && I.swaps != nullptr) {

@@ -90,7 +90,7 @@ class QmgRouteResult(C.Structure):
 
 class QmgRouteOptions(C.Structure):
     _fields_ = [("pool_nodes", C.c_uint32), ("threads_per_search", C.c_uint32),
-                ("searches_per_sm", C.c_uint32), ("_pad", C.c_uint32)]
+                ("searches_per_sm", C.c_uint32), ("lean_outputs", C.c_uint32)]
 
 
 class QmgRouteStats(C.Structure):

@@ -97,10 +97,9 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
   std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8);
   std::vector<OpenEntry> open(poolNodes);
   std::vector<uint64_t> table(tableSize, 0);
-  std::vector<int16_t> ql(4 * static_cast<size_t>(n));
-  std::vector<uint32_t> consMask((n + 31) / 32 + 1);
-  std::vector<Child> ch(kChunk);
-  std::vector<double> lookPen(kChunk / 2 * kLookBlock);
+  Scratch S = scratchLayout(n);
+  std::vector<uint64_t> scratch(S.bytes / 8 + 1);
+  S.base = reinterpret_cast<uint8_t*>(scratch.data());
   uint32_t stamp = 0;
   for (size_t ii = 0; ii < nInstances; ++ii) {
     const qmg_instance& in = instances[ii];
@@ -157,14 +156,6 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.tableMask = tableSize - 1;
     M.stamp = stamp;
     M.maxG = fc.maxG;
-    Scratch S{};
-    S.Q = ql.data();
-    S.L = ql.data() + n;
-    S.curQ = ql.data() + 2 * n;
-    S.curL = ql.data() + 3 * n;
-    S.consMask = consMask.data();
-    S.ch = ch.data();
-    S.lookPen = lookPen.data();
     InstView I{};
     I.circ = cv;
     I.initLoc = in.initial_locations;
