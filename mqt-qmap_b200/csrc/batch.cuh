@@ -147,26 +147,33 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   const bool fid = b->cfg.fidelityAware != 0;
   StageClock sc;
 
-  // ---- unique circuits (instances that point at the same layers share one)
-  std::unordered_map<CircKey, uint32_t, CircKeyHash> seen;
-  seen.reserve(nInst * 2);
+  // ---- unique circuits (instances that point at the same layers share one):
+  // open-addressing table keyed by the caller's array pointers
   std::vector<CircSlot> circs;
   std::vector<const qmg_layers*> circSrc;
+  std::vector<CircKey> circKey;
   std::vector<uint32_t> circOf(nInst);
-  size_t sumOff = 0, sumL = 0, sumG2 = 0, sumG1 = 0, sumCons = 0;
+  size_t tabSize = 64;
+  while (tabSize < 2 * nInst) {
+    tabSize <<= 1;
+  }
+  std::vector<uint32_t> tab(tabSize, 0);  // circuit index + 1
   for (size_t i = 0; i < nInst; ++i) {
     const qmg_layers& L = instances[i].layers;
     if (L.n_layers > 0 &&
         (L.gate2q_offsets == nullptr ||
-         (L.gates2q == nullptr && L.gate2q_offsets[L.n_layers] > 0) ||
          (L.gate1q_offsets != nullptr && L.gates1q == nullptr &&
           L.gate1q_offsets[L.n_layers] > 0))) {
       return fail(QMG_BAD_ARG, "instance without layers");
     }
     const CircKey key{L.gate2q_offsets, L.gates2q, L.gate1q_offsets, L.gates1q,
                       L.n_layers};
-    auto it = seen.find(key);
-    if (it == seen.end()) {
+    size_t slot = CircKeyHash()(key) & (tabSize - 1);
+    uint32_t hit = 0;
+    while ((hit = tab[slot]) != 0 && !(circKey[hit - 1] == key)) {
+      slot = (slot + 1) & (tabSize - 1);
+    }
+    if (hit == 0) {
       CircSlot c;
       c.nLayers = L.n_layers;
       c.nLogical = L.n_logical;
@@ -174,21 +181,16 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       c.nG1 = (L.n_layers > 0 && L.gate1q_offsets != nullptr)
                   ? L.gate1q_offsets[L.n_layers]
                   : 0;
-      c.offOff = sumOff;
-      c.layerOff = sumL;
-      c.g2Off = sumG2;
-      c.g1Off = sumG1;
-      c.consOff = sumCons;
-      sumOff += static_cast<size_t>(L.n_layers) + 1;
-      sumL += L.n_layers;
-      sumG2 += c.nG2;
-      sumG1 += c.nG1;
-      sumCons += 2 * c.nG2 + c.nG1;
-      it = seen.emplace(key, static_cast<uint32_t>(circs.size())).first;
+      if (c.nG2 > 0 && L.gates2q == nullptr) {
+        return fail(QMG_BAD_ARG, "instance without layers");
+      }
       circs.push_back(c);
       circSrc.push_back(&L);
+      circKey.push_back(key);
+      hit = static_cast<uint32_t>(circs.size());
+      tab[slot] = hit;
     }
-    circOf[i] = it->second;
+    circOf[i] = hit - 1;
   }
 
   sc.mark("dedupe");
@@ -278,13 +280,14 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   }
 
   sc.mark("geometry");
-  // ---- input arena layout
+  // ---- input arena layout: circuits first (each contiguous), then the
+  // per-instance sections
   Layout li;
-  const size_t sG2Off = li.add(sumOff * 4), sG1Off = li.add(sumOff * 4),
-               sConsOff = li.add(sumOff * 4), sG2 = li.add(sumG2 * sizeof(Gate2)),
-               sG1 = li.add(sumG1 * sizeof(Gate1)), sCons = li.add(sumCons * 2),
-               sTwoQ = li.add(sumL * 4), sFirst = li.add(sumL * 4),
-               sSplit = li.add(sumL), sInit = li.add(nInst * n * 2),
+  for (auto& c : circs) {
+    c.place(li);
+  }
+  const size_t circBytes = li.size;
+  const size_t sInit = li.add(nInst * n * 2),
                sFactors = li.add(static_cast<size_t>(cfg->nr_lookaheads) * 8);
   b->iInst = li.add(nInst * sizeof(InstView));
   b->iOrder = li.add(nInst * 4);
@@ -327,24 +330,69 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   uint8_t* D = W.in.p;
 
   sc.mark("alloc");
-  // ---- flatten the circuits into the pinned arena (host threads)
-  std::atomic<int> bad{0};
-  parallelFor(circs.size(), 16, [&](size_t ci) {
+  // ---- flatten the circuits into the pinned arena (host threads); the arena
+  // is cut into ranges of circuits and the thread that completes a range
+  // starts its host-to-device copy, so the copies overlap the flattening
+  const size_t nC = circs.size();
+  const size_t nChunks =
+      std::min<size_t>(16, std::max<size_t>(1, circBytes >> 22));
+  std::vector<uint32_t> chunkOf(nC);
+  std::vector<size_t> chunkBegin(nChunks + 1, circBytes);
+  std::unique_ptr<std::atomic<uint32_t>[]> chunkLeft(
+      new std::atomic<uint32_t>[nChunks]);
+  {
+    std::vector<uint32_t> cnt(nChunks, 0);
+    const size_t per = (circBytes + nChunks - 1) / nChunks;
+    size_t k = 0;
+    chunkBegin[0] = 0;
+    for (size_t ci = 0; ci < nC; ++ci) {
+      const size_t at0 = circs[ci].bG2Off;
+      while (k + 1 < nChunks && at0 >= (k + 1) * per) {
+        ++k;
+        chunkBegin[k] = at0;
+      }
+      chunkOf[ci] = static_cast<uint32_t>(k);
+      ++cnt[k];
+    }
+    for (size_t q = k + 1; q < nChunks; ++q) {
+      chunkBegin[q] = circBytes;
+    }
+    for (size_t q = 0; q < nChunks; ++q) {
+      chunkLeft[q].store(cnt[q]);
+    }
+  }
+  std::atomic<int> bad{0}, copyErr{0};
+  const int device = arch->device;
+  parallelFor(nC, 16, [&](size_t ci) {
     CircSlot& c = circs[ci];
     const qmg_layers& L = *circSrc[ci];
     if (!flattenCircuit(
             n, fid, L.gate2q_offsets, reinterpret_cast<const Gate2*>(L.gates2q),
             L.gate1q_offsets, reinterpret_cast<const Gate1*>(L.gates1q), c,
-            at<uint32_t>(H, sG2Off) + c.offOff, at<Gate2>(H, sG2) + c.g2Off,
-            at<uint32_t>(H, sG1Off) + c.offOff, at<Gate1>(H, sG1) + c.g1Off,
-            at<uint32_t>(H, sConsOff) + c.offOff, at<uint16_t>(H, sCons) + c.consOff,
-            at<uint32_t>(H, sTwoQ) + c.layerOff, at<uint32_t>(H, sFirst) + c.layerOff,
-            at<uint8_t>(H, sSplit) + c.layerOff)) {
+            at<uint32_t>(H, c.bG2Off), at<Gate2>(H, c.bG2),
+            at<uint32_t>(H, c.bG1Off), at<Gate1>(H, c.bG1),
+            at<uint32_t>(H, c.bConsOff), at<uint16_t>(H, c.bCons),
+            at<uint32_t>(H, c.bTwoQ), at<uint32_t>(H, c.bFirst),
+            at<uint8_t>(H, c.bSplit))) {
       bad.store(1);
+    }
+    const uint32_t k = chunkOf[ci];
+    if (chunkLeft[k].fetch_sub(1) == 1) {
+      const size_t lo = chunkBegin[k], hi = chunkBegin[k + 1];
+      if (hi > lo) {
+        if (cudaSetDevice(device) != cudaSuccess ||
+            cudaMemcpyAsync(D + lo, H + lo, hi - lo, cudaMemcpyHostToDevice,
+                            s) != cudaSuccess) {
+          copyErr.store(1);
+        }
+      }
     }
   });
   if (bad.load() != 0) {
     return fail(QMG_BAD_ARG, "gate operand out of range");
+  }
+  if (copyErr.load() != 0) {
+    return fail(QMG_CUDA_ERROR, cudaGetErrorString(cudaGetLastError()));
   }
   sc.mark("flatten");
   uint32_t maxG = 1;
@@ -385,16 +433,16 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     std::memset(&I, 0, sizeof(I));
     I.circ.nLayers = c.nLayers;
     I.circ.nLogical = c.nLogical;
-    I.circ.g2Off = at<uint32_t>(D, sG2Off) + c.offOff;
-    I.circ.g2 = at<Gate2>(D, sG2) + c.g2Off;
-    I.circ.g1Off = at<uint32_t>(D, sG1Off) + c.offOff;
-    I.circ.g1 = at<Gate1>(D, sG1) + c.g1Off;
-    I.circ.consOff = at<uint32_t>(D, sConsOff) + c.offOff;
-    I.circ.cons = at<uint16_t>(D, sCons) + c.consOff;
-    I.circ.twoQ = at<uint32_t>(D, sTwoQ) + c.layerOff;
-    I.circ.firstAfter = at<uint32_t>(D, sFirst) + c.layerOff;
+    I.circ.g2Off = at<uint32_t>(D, c.bG2Off);
+    I.circ.g2 = at<Gate2>(D, c.bG2);
+    I.circ.g1Off = at<uint32_t>(D, c.bG1Off);
+    I.circ.g1 = at<Gate1>(D, c.bG1);
+    I.circ.consOff = at<uint32_t>(D, c.bConsOff);
+    I.circ.cons = at<uint16_t>(D, c.bCons);
+    I.circ.twoQ = at<uint32_t>(D, c.bTwoQ);
+    I.circ.firstAfter = at<uint32_t>(D, c.bFirst);
     I.circ.nTwoQ = c.nTwoQ;
-    I.circ.splittable = at<uint8_t>(D, sSplit) + c.layerOff;
+    I.circ.splittable = at<uint8_t>(D, c.bSplit);
     I.initLoc = at<int16_t>(D, sInit) + i * n;
     I.passes = instances[i].bidirectional_passes;
     I.firstLayer = instances[i].first_layer;
@@ -457,7 +505,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     }
   }
   sc.mark("views");
-  CU(cudaMemcpyAsync(D, H, b->inSize, cudaMemcpyHostToDevice, s));
+  // (the circuit ranges are already on their way)
+  CU(cudaMemcpyAsync(D + circBytes, H + circBytes, b->inSize - circBytes,
+                     cudaMemcpyHostToDevice, s));
   CU(cudaMemsetAsync(Wk + b->tableOff, 0, b->tableBytes, s));
   b->h2dBytes = b->inSize;
   {

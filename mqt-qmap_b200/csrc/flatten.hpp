@@ -72,14 +72,28 @@ struct Layout {
   }
 };
 
-// where one circuit's arrays live (element offsets into the typed sections)
+// where one circuit's arrays live: byte offsets into the staging arena (each
+// circuit's sections are contiguous, so a range of circuits is one range of
+// bytes and can be copied to the device as soon as it is filled)
 struct CircSlot {
   uint32_t nLayers = 0, nLogical = 0;
   size_t nG2 = 0, nG1 = 0;
-  size_t layerOff = 0;  // into the per-layer sections (g2Off has +1 per circuit)
-  size_t offOff = 0;    // into the (nLayers + 1)-sized offset sections
-  size_t g2Off = 0, g1Off = 0, consOff = 0;  // element offsets of the payloads
+  size_t bG2Off = 0, bG1Off = 0, bConsOff = 0, bG2 = 0, bG1 = 0, bCons = 0,
+         bTwoQ = 0, bFirst = 0, bSplit = 0, bEnd = 0;
   uint32_t nTwoQ = 0, maxG = 1;
+  void place(Layout& lay) {
+    const size_t nOff = static_cast<size_t>(nLayers) + 1;
+    bG2Off = lay.add(nOff * 4);
+    bG1Off = lay.add(nOff * 4);
+    bConsOff = lay.add(nOff * 4);
+    bG2 = lay.add(nG2 * sizeof(Gate2));
+    bG1 = lay.add(nG1 * sizeof(Gate1));
+    bCons = lay.add((2 * nG2 + nG1) * 2);
+    bTwoQ = lay.add(static_cast<size_t>(nLayers) * 4);
+    bFirst = lay.add(static_cast<size_t>(nLayers) * 4);
+    bSplit = lay.add(nLayers);
+    bEnd = lay.size;
+  }
 };
 
 // derive the kernel's per-layer tables for one circuit.  Returns false when a
