@@ -217,6 +217,8 @@ def main():
                     "circuits_per_s": sample / busy,
                     "search_loop_only_nodes_per_core_s": exp / search_s if search_s else None}
 
+    # one process per GPU shares the host cores for staging
+    os.environ.setdefault("QMAP_B200_THREADS", str(max(2, cores // max(1, world))))
     import torch
     import torch.distributed as dist
     from qmap_b200 import _abi, routing

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -17,12 +18,24 @@
 
 namespace qmg {
 
+// host threads used for staging: QMAP_B200_THREADS, else the hardware
+// concurrency (one process per GPU shares the host: launchers should set the
+// variable to cores / ranks)
 inline unsigned hostThreads() {
-  unsigned t = std::thread::hardware_concurrency();
-  if (t == 0) {
-    t = 4;
-  }
-  return std::min(t, 32U);
+  static const unsigned cached = [] {
+    unsigned t = 0;
+    if (const char* e = std::getenv("QMAP_B200_THREADS")) {
+      t = static_cast<unsigned>(std::strtoul(e, nullptr, 10));
+    }
+    if (t == 0) {
+      t = std::thread::hardware_concurrency();
+    }
+    if (t == 0) {
+      t = 4;
+    }
+    return std::min(t, 64U);
+  }();
+  return cached;
 }
 
 // f(i) for i in [0, n) on up to hostThreads() threads, dynamic chunks

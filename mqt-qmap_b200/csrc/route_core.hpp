@@ -1567,8 +1567,11 @@ template <int H> struct Search {
       ++M.stamp;  // (M lives in shared memory on the device)
     }
     g.sync();
+    // layers are only split in the final pass (the host splits and resumes;
+    // a pseudo-routing pass searches on - the reference would split there too
+    // and undo it afterwards, :309-344)
     const bool splittable =
-        C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
+        record && C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
     // one loop iteration = evaluate one chunk of nodes (first the root from
     // the mapper's current layout, then the children of the node being
     // expanded) and push them; when a parent is exhausted the next node is

@@ -3,3 +3,4 @@ from ._abi import QmapError  # noqa: F401
 from .architecture import Architecture, Properties  # noqa: F401
 from .circuit import Circuit, load_qasm, parse_qasm  # noqa: F401
 from .routing import make_config  # noqa: F401
+from .mapper import HeuristicMapper, MappingResults, verify_mapping  # noqa: F401

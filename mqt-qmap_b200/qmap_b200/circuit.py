@@ -70,6 +70,9 @@ class Circuit:
         leaves the highest logical qubit(s) unplaced until their first gate,
         which the golden layouts of 4gt11_84 in the reference's
         test_heuristic.cpp pin."""
+        if any(op.name == "swap" for op in self.ops):
+            raise ValueError("Circuit contains SWAP gates. Please make sure that the input "
+                             "circuit's gates are decomposed to the appropriate gate set!")
         used = self.used_qubits()
         rank = {q: i for i, q in enumerate(used)}
         c, t = self.gate_arrays()
@@ -233,6 +236,9 @@ def parse_qasm(text: str, name: str = "circuit") -> Circuit:
             if len(qs) != 1:
                 raise ValueError(f"bad 1q gate: {s!r}")
             circ.ops.append(Op(g, (qs[0],), ps))
+        elif g == "swap" and len(qs) == 2:
+            # only in mapped circuits; the mapper itself wants SWAPs decomposed
+            circ.ops.append(Op("swap", (qs[0], qs[1])))
         else:
             # Mapper::createLayers :157-161: gates with more than one control
             raise ValueError(

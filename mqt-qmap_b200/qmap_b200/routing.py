@@ -86,11 +86,22 @@ class LayeredCircuit:
             self.n, len(self.control), self.control.ctypes.data,
             self.target.ctypes.data, int(layering), C.byref(h)))
         self.h = h
+        self.layering = int(layering)
+        self.splits = []  # layers split so far, in order
 
     def __del__(self):
         if getattr(self, "h", None):
             self.lib.qmg_circuit_destroy(self.h)
             self.h = None
+
+    def split_copy(self, layer: int) -> "LayeredCircuit":
+        """A new circuit with the same gates and split history plus a split of
+        `layer` (Mapper::splitLayer); this object is left untouched, other
+        routing instances may share it."""
+        out = LayeredCircuit(self.lib, self.n, self.control, self.target, self.layering)
+        for l in self.splits + [int(layer)]:
+            out.split(l)
+        return out
 
     @property
     def layers(self) -> QmgLayers:
@@ -119,6 +130,7 @@ class LayeredCircuit:
 
     def split(self, layer: int):
         _abi.check(self.lib, self.lib.qmg_circuit_split_layer(self.h, layer))
+        self.splits.append(int(layer))
 
 
 @dataclass

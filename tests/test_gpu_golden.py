@@ -134,3 +134,27 @@ def test_workspace_is_reused_between_batches():
         assert o.status == 0
         assert np.array_equal(o.swaps, first[0].swaps)
         assert o.expanded_nodes == first[0].expanded_nodes
+
+
+def test_mapper_mirror_on_cuda():
+    """HeuristicMapper.map() end to end on the CUDA library: routed circuits
+    verify against the input, SWAP counts equal the reference's, a low split
+    limit exercises split-and-resume."""
+    from qmap_b200 import mapper
+    a = arch_for("ibm_qx5")
+    checked = 0
+    for g in RUNS:
+        if g.meta["arch"] != "ibm_qx5" or g.generated_nodes > 20000:
+            continue
+        circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
+        m = mapper.HeuristicMapper(circ, a)
+        res = m.map(**g.meta["config"])
+        assert mapper.verify_mapping(circ, m) == "", g.label
+        assert res.output_swaps == g.swaps, g.label
+        checked += 1
+    assert checked > 40
+    circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, "qft_16.qasm"))
+    m = mapper.HeuristicMapper(circ, a)
+    res = m.map(layering="disjoint_qubits", automatic_layer_splits_node_limit=3)
+    assert res.layer_splits > 0
+    assert mapper.verify_mapping(circ, m) == ""

@@ -1,0 +1,96 @@
+"""CPU suite: the host mirror of HeuristicMapper (qmap_b200/mapper.py) - initial
+layouts, split-and-resume, circuit emission, verifier - driven through the
+host debug build of the kernel source; SWAP counts are checked against the
+committed outputs of the reference."""
+import os
+
+import numpy as np
+import pytest
+
+import emu_backend
+import parity
+from qmap_b200 import _abi, mapper, routing
+from qmap_b200 import architecture as ar
+from qmap_b200 import circuit as qcirc
+
+T = parity.golden_tables()
+_cache = {}
+
+
+def arch_and_backend(name):
+    if name not in _cache:
+        n, e = parity.read_arch_file(name)
+        a = ar.Architecture(n, [tuple(int(v) for v in x) for x in e])
+        be = emu_backend.EmuBackend(n, e, T[f"{name}_dist"], T[f"{name}_dist_rev"],
+                                    pool_nodes=1 << 17)
+        _cache[name] = (a, be)
+    return _cache[name]
+
+
+CASES = [g for g in parity.golden_runs()
+         if g.meta["calibration"] is None and g.generated_nodes <= 20000][::3]
+
+
+def test_mapped_circuits_verify_and_match_reference_swap_counts():
+    assert len(CASES) > 60
+    bad = []
+    n_split = 0
+    for g in CASES:
+        a, be = arch_and_backend(g.meta["arch"])
+        circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
+        m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+        res = m.map(**g.meta["config"])
+        msg = mapper.verify_mapping(circ, m)
+        if msg:
+            bad.append((g.label, msg))
+            continue
+        if g.meta["split"]:
+            n_split += 1
+            # (pseudo-routing passes are not split by the product, so with
+            # bidirectional passes the reference may have split only there)
+            if res.layer_splits == 0 and not g.meta["config"].get(
+                    "iterative_bidirectional_routing_passes"):
+                bad.append((g.label, "reference split a layer, the mapper did not"))
+        elif res.output_swaps != g.swaps:
+            # (swap_on_first_layer is off: the first layer's SWAPs fold into
+            # the initial layout in both implementations)
+            bad.append((g.label, f"swaps {res.output_swaps} != {g.swaps}"))
+    assert not bad, bad[:5]
+    assert n_split >= 5
+
+
+def test_static_and_identity_layouts():
+    a, be = arch_and_backend("ibm_qx5")
+    circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, "rd32-v0_66.qasm"))
+    for layout in ("identity", "static", "dynamic"):
+        m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+        res = m.map(initial_layout=layout)
+        assert mapper.verify_mapping(circ, m) == ""
+        assert res.output_cnots == res.input_cnots
+        assert res.output_gates == (res.input_gates + res.output_swaps
+                                    + 4 * res.output_direction_reverse)
+        out = m.mapped_circuit()
+        again = qcirc.parse_qasm(out.to_qasm())
+        assert len(again.ops) == len(out.ops)
+
+
+def test_parameter_checks_use_the_reference_messages():
+    a, be = arch_and_backend("ibm_qx4")
+    circ = qcirc.Circuit(2)
+    circ.cx(0, 1)
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    with pytest.raises(_abi.QmapError, match="not suitable for heuristic mapper"):
+        m.map(layering="odd_gates")
+    with pytest.raises(_abi.QmapError, match="calibration data"):
+        m.map(heuristic="fidelity_best_location", lookahead_heuristic="none")
+
+
+def test_verifier_rejects_a_wrong_circuit():
+    a, be = arch_and_backend("ibm_qx5")
+    circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, "4mod5-v0_20.qasm"))
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    m.map()
+    assert mapper.verify_mapping(circ, m) == ""
+    k = next(i for i, o in enumerate(m.mapped_ops) if o.name == "swap")
+    del m.mapped_ops[k]
+    assert mapper.verify_mapping(circ, m) != ""
