@@ -10,6 +10,7 @@
 #include <mutex>
 #include <unordered_map>
 
+#include "derive.cuh"
 #include "staging.hpp"
 
 using qmg_workspace = qmg::Workspace;
@@ -284,15 +285,23 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   // per-instance sections
   Layout li;
   for (auto& c : circs) {
-    c.place(li);
+    c.placeUpload(li);
   }
   const size_t circBytes = li.size;
   const size_t sInit = li.add(nInst * n * 2),
                sFactors = li.add(static_cast<size_t>(cfg->nr_lookaheads) * 8);
+  const size_t sDerive = li.add(circs.size() * sizeof(DeriveView));
   b->iInst = li.add(nInst * sizeof(InstView));
   b->iOrder = li.add(nInst * 4);
   b->iMem = li.add(static_cast<size_t>(nWarps) * sizeof(SearchMem));
   b->inSize = li.size;
+  // device-only tail of the input arena: the tables derived on the device
+  Layout ld;
+  ld.size = b->inSize;
+  for (auto& c : circs) {
+    c.placeDerived(ld);
+  }
+  const size_t inTotal = ld.size;
 
   // ---- output arena layout
   Layout lo;
@@ -324,7 +333,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   if (!W.hin.ensure(b->inSize) || !W.hout.ensure(pinnedOut)) {
     return fail(QMG_OOM, "pinned host allocation failed");
   }
-  CU(W.in.ensure(b->inSize));
+  CU(W.in.ensure(inTotal));
   CU(W.out.ensure(b->outSize));
   uint8_t* H = W.hin.p;
   uint8_t* D = W.in.p;
@@ -366,16 +375,26 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   parallelFor(nC, 16, [&](size_t ci) {
     CircSlot& c = circs[ci];
     const qmg_layers& L = *circSrc[ci];
-    if (!flattenCircuit(
-            n, fid, L.gate2q_offsets, reinterpret_cast<const Gate2*>(L.gates2q),
-            L.gate1q_offsets, reinterpret_cast<const Gate1*>(L.gates1q), c,
-            at<uint32_t>(H, c.bG2Off), at<Gate2>(H, c.bG2),
-            at<uint32_t>(H, c.bG1Off), at<Gate1>(H, c.bG1),
-            at<uint32_t>(H, c.bConsOff), at<uint16_t>(H, c.bCons),
-            at<uint32_t>(H, c.bTwoQ), at<uint32_t>(H, c.bFirst),
-            at<uint8_t>(H, c.bSplit))) {
+    if (!stageCircuit(n, L.gate2q_offsets,
+                      reinterpret_cast<const Gate2*>(L.gates2q),
+                      L.gate1q_offsets,
+                      reinterpret_cast<const Gate1*>(L.gates1q), c,
+                      at<uint32_t>(H, c.bG2Off), at<Gate2>(H, c.bG2),
+                      at<uint32_t>(H, c.bG1Off), at<Gate1>(H, c.bG1))) {
       bad.store(1);
     }
+    DeriveView& dv = at<DeriveView>(H, sDerive)[ci];
+    dv.nLayers = c.nLayers;
+    dv.fidelityAware = fid ? 1U : 0U;
+    dv.g2Off = at<uint32_t>(D, c.bG2Off);
+    dv.g2 = at<Gate2>(D, c.bG2);
+    dv.g1Off = at<uint32_t>(D, c.bG1Off);
+    dv.g1 = at<Gate1>(D, c.bG1);
+    dv.cons = at<uint16_t>(D, c.dCons);
+    dv.consCnt = at<uint16_t>(D, c.dConsCnt);
+    dv.twoQ = at<uint32_t>(D, c.dTwoQ);
+    dv.firstAfter = at<uint32_t>(D, c.dFirst);
+    dv.split = at<uint8_t>(D, c.dSplit);
     const uint32_t k = chunkOf[ci];
     if (chunkLeft[k].fetch_sub(1) == 1) {
       const size_t lo = chunkBegin[k], hi = chunkBegin[k + 1];
@@ -389,7 +408,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     }
   });
   if (bad.load() != 0) {
-    return fail(QMG_BAD_ARG, "gate operand out of range");
+    return fail(QMG_BAD_ARG, "malformed layers (offsets or gate operands)");
   }
   if (copyErr.load() != 0) {
     return fail(QMG_CUDA_ERROR, cudaGetErrorString(cudaGetLastError()));
@@ -437,12 +456,13 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.circ.g2 = at<Gate2>(D, c.bG2);
     I.circ.g1Off = at<uint32_t>(D, c.bG1Off);
     I.circ.g1 = at<Gate1>(D, c.bG1);
-    I.circ.consOff = at<uint32_t>(D, c.bConsOff);
-    I.circ.cons = at<uint16_t>(D, c.bCons);
-    I.circ.twoQ = at<uint32_t>(D, c.bTwoQ);
-    I.circ.firstAfter = at<uint32_t>(D, c.bFirst);
+    I.circ.consOff = nullptr;
+    I.circ.cons = at<uint16_t>(D, c.dCons);
+    I.circ.consCnt = at<uint16_t>(D, c.dConsCnt);
+    I.circ.twoQ = at<uint32_t>(D, c.dTwoQ);
+    I.circ.firstAfter = at<uint32_t>(D, c.dFirst);
     I.circ.nTwoQ = c.nTwoQ;
-    I.circ.splittable = at<uint8_t>(D, c.bSplit);
+    I.circ.splittable = at<uint8_t>(D, c.dSplit);
     I.initLoc = at<int16_t>(D, sInit) + i * n;
     I.passes = instances[i].bidirectional_passes;
     I.firstLayer = instances[i].first_layer;
@@ -508,6 +528,11 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   // (the circuit ranges are already on their way)
   CU(cudaMemcpyAsync(D + circBytes, H + circBytes, b->inSize - circBytes,
                      cudaMemcpyHostToDevice, s));
+  if (!circs.empty()) {
+    derive_circuit_tables<<<static_cast<unsigned>(circs.size()), 128, 0, s>>>(
+        at<DeriveView>(D, sDerive), static_cast<uint32_t>(circs.size()));
+    CU(cudaGetLastError());
+  }
   CU(cudaMemsetAsync(Wk + b->tableOff, 0, b->tableBytes, s));
   b->h2dBytes = b->inSize;
   {

@@ -85,29 +85,75 @@ struct Layout {
   }
 };
 
-// where one circuit's arrays live: byte offsets into the staging arena (each
-// circuit's sections are contiguous, so a range of circuits is one range of
-// bytes and can be copied to the device as soon as it is filled)
+// where one circuit's arrays live.  Uploaded part (byte offsets into the
+// staging arena; each circuit's sections are contiguous, so a range of
+// circuits is one range of bytes and can be copied to the device as soon as
+// it is filled): the CSR layers as the caller gave them.  Derived part (byte
+// offsets into a device-only arena): the tables derive.cuh computes.
 struct CircSlot {
   uint32_t nLayers = 0, nLogical = 0;
   size_t nG2 = 0, nG1 = 0;
-  size_t bG2Off = 0, bG1Off = 0, bConsOff = 0, bG2 = 0, bG1 = 0, bCons = 0,
-         bTwoQ = 0, bFirst = 0, bSplit = 0, bEnd = 0;
+  size_t bG2Off = 0, bG1Off = 0, bG2 = 0, bG1 = 0, bEnd = 0;
+  size_t dCons = 0, dConsCnt = 0, dTwoQ = 0, dFirst = 0, dSplit = 0;
   uint32_t nTwoQ = 0, maxG = 1;
-  void place(Layout& lay) {
+  void placeUpload(Layout& lay) {
     const size_t nOff = static_cast<size_t>(nLayers) + 1;
     bG2Off = lay.add(nOff * 4);
     bG1Off = lay.add(nOff * 4);
-    bConsOff = lay.add(nOff * 4);
     bG2 = lay.add(nG2 * sizeof(Gate2));
     bG1 = lay.add(nG1 * sizeof(Gate1));
-    bCons = lay.add((2 * nG2 + nG1) * 2);
-    bTwoQ = lay.add(static_cast<size_t>(nLayers) * 4);
-    bFirst = lay.add(static_cast<size_t>(nLayers) * 4);
-    bSplit = lay.add(nLayers);
     bEnd = lay.size;
   }
+  void placeDerived(Layout& lay) {
+    dCons = lay.add((2 * nG2 + nG1) * 2);
+    dConsCnt = lay.add(static_cast<size_t>(nLayers) * 2);
+    dTwoQ = lay.add(static_cast<size_t>(nLayers) * 4);
+    dFirst = lay.add(static_cast<size_t>(nLayers) * 4);
+    dSplit = lay.add(nLayers);
+  }
 };
+
+// copy one circuit's CSR layers into the staging arena, validating them on the
+// way (monotone offsets, operands in range); fills nTwoQ and maxG.
+inline bool stageCircuit(int n, const uint32_t* off2, const Gate2* g2,
+                         const uint32_t* off1, const Gate1* g1, CircSlot& s,
+                         uint32_t* oG2Off, Gate2* oG2, uint32_t* oG1Off,
+                         Gate1* oG1) {
+  const uint32_t nL = s.nLayers;
+  std::memcpy(oG2Off, off2, (static_cast<size_t>(nL) + 1) * 4);
+  if (s.nG2 > 0) {
+    std::memcpy(oG2, g2, s.nG2 * sizeof(Gate2));
+  }
+  if (off1 != nullptr) {
+    std::memcpy(oG1Off, off1, (static_cast<size_t>(nL) + 1) * 4);
+    if (s.nG1 > 0) {
+      std::memcpy(oG1, g1, s.nG1 * sizeof(Gate1));
+    }
+  } else {
+    std::memset(oG1Off, 0, (static_cast<size_t>(nL) + 1) * 4);
+  }
+  uint32_t ntq = 0, maxG = 1;
+  bool ok = nL == 0 || (oG2Off[0] == 0 && oG1Off[0] == 0);
+  for (uint32_t l = 0; l < nL; ++l) {
+    ok = ok && oG2Off[l + 1] >= oG2Off[l] && oG1Off[l + 1] >= oG1Off[l];
+    const uint32_t G = oG2Off[l + 1] - oG2Off[l];
+    maxG = std::max(maxG, G);
+    ntq += G > 0 ? 1U : 0U;
+  }
+  ok = ok && (nL == 0 || (oG2Off[nL] == s.nG2 && oG1Off[nL] == s.nG1));
+  uint32_t worst = 0;
+  bool same = false;
+  for (size_t i = 0; i < s.nG2; ++i) {
+    worst = std::max<uint32_t>(worst, std::max(oG2[i].q1, oG2[i].q2));
+    same = same || oG2[i].q1 == oG2[i].q2;
+  }
+  for (size_t i = 0; i < s.nG1; ++i) {
+    worst = std::max<uint32_t>(worst, oG1[i].q);
+  }
+  s.nTwoQ = ntq;
+  s.maxG = maxG;
+  return ok && !same && (s.nG2 + s.nG1 == 0 || worst < static_cast<uint32_t>(n));
+}
 
 // derive the kernel's per-layer tables for one circuit.  Returns false when a
 // gate operand is out of range.

@@ -24,7 +24,15 @@
 #define QMG_HD __host__ __device__ __forceinline__
 #define QMG_D __device__ __forceinline__
 #define QMG_NOUNROLL _Pragma("unroll 1")
+// (measured: out-of-line reductions cost 6 % on config 2, so the default is
+// inline; -DQMG_OUTLINE_REDUCTIONS keeps the experiment buildable)
+#if defined(QMG_OUTLINE_REDUCTIONS)
+#define QMG_HD_RED __host__ __device__ __noinline__
 #else
+#define QMG_HD_RED QMG_HD
+#endif
+#else
+#define QMG_HD_RED inline
 #define QMG_HD inline
 #define QMG_D inline
 #define QMG_NOUNROLL
@@ -97,8 +105,12 @@ struct CircView {
   const Gate2* g2;
   const uint32_t* g1Off;
   const Gate1* g1;
-  const uint32_t* consOff;  // getConsideredQubits(layer), ascending
+  // getConsideredQubits(layer), ascending: either a CSR (consOff) or, when
+  // consOff is null, at most 2G+G1 entries from 2*g2Off[l]+g1Off[l] with
+  // their number in consCnt[l] (the layout the device derives itself)
+  const uint32_t* consOff;
   const uint16_t* cons;
+  const uint16_t* consCnt;
   // Mapper::getNextLayer (src/sc/Mapper.cpp:437-448) in closed form: twoQ is
   // the ascending list of layers holding a 2q gate, firstAfter[l] the index in
   // twoQ of the first such layer > l
@@ -336,26 +348,48 @@ QMG_HD Gate1 ldGate1(const Gate1* p) {
 #endif
 }
 
-QMG_HD double gmin(const Group& g, double v) {
+QMG_HD_RED double gminV(double v) {
+  const Group g;
   for (int d = Group::W / 2; d > 0; d >>= 1) {
     const double o = g.xorv(v, d);
     v = o < v ? o : v;
   }
   return v;
 }
-QMG_HD double gmax(const Group& g, double v) {
+QMG_HD_RED double gmaxV(double v) {
+  const Group g;
   for (int d = Group::W / 2; d > 0; d >>= 1) {
     const double o = g.xorv(v, d);
     v = o > v ? o : v;
   }
   return v;
 }
-QMG_HD uint64_t gsum64(const Group& g, uint64_t v) {
+QMG_HD_RED uint64_t gsum64V(uint64_t v) {
+  const Group g;
   for (int d = Group::W / 2; d > 0; d >>= 1) {
     v += g.xorv(v, d);
   }
   return v;
 }
+QMG_HD_RED uint32_t gmaxU32V(uint32_t v) {
+  const Group g;
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    const uint32_t o = g.xorv(v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+QMG_HD_RED uint64_t gmaxU64V(uint64_t v) {
+  const Group g;
+  for (int d = Group::W / 2; d > 0; d >>= 1) {
+    const uint64_t o = g.xorv(v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+QMG_HD double gmin(const Group&, double v) { return gminV(v); }
+QMG_HD double gmax(const Group&, double v) { return gmaxV(v); }
+QMG_HD uint64_t gsum64(const Group&, uint64_t v) { return gsum64V(v); }
 // (value, index) argmin; ties -> smallest index ("first strict minimum")
 QMG_HD void gargmin(const Group& g, double& v, uint32_t& i) {
   for (int d = Group::W / 2; d > 0; d >>= 1) {
@@ -983,20 +1017,8 @@ template <int H> struct Search {
     return false;
   }
 
-  QMG_HD uint32_t gmaxU32(uint32_t v) const {
-    for (int d = Group::W / 2; d > 0; d >>= 1) {
-      const uint32_t o = g.xorv(v, d);
-      v = o > v ? o : v;
-    }
-    return v;
-  }
-  QMG_HD uint64_t gmaxU64(uint64_t v) const {
-    for (int d = Group::W / 2; d > 0; d >>= 1) {
-      const uint64_t o = g.xorv(v, d);
-      v = o > v ? o : v;
-    }
-    return v;
-  }
+  QMG_HD uint32_t gmaxU32(uint32_t v) const { return gmaxU32V(v); }
+  QMG_HD uint64_t gmaxU64(uint64_t v) const { return gmaxU64V(v); }
 
   // position of the top of the open list (group-uniform result).  Every lane
   // reduces its strided share with the pairwise order; the lanes' winners are
@@ -1526,9 +1548,14 @@ template <int H> struct Search {
     const uint32_t lo1 = ldg(I.circ.g1Off + l);
     G1 = ldg(I.circ.g1Off + l + 1) - lo1;
     gates1 = I.circ.g1 + lo1;
-    const uint32_t loc = ldg(I.circ.consOff + l);
-    nCons = ldg(I.circ.consOff + l + 1) - loc;
-    cons = I.circ.cons + loc;
+    if (I.circ.consOff != nullptr) {
+      const uint32_t loc = ldg(I.circ.consOff + l);
+      nCons = ldg(I.circ.consOff + l + 1) - loc;
+      cons = I.circ.cons + loc;
+    } else {
+      nCons = ldg(I.circ.consCnt + l);
+      cons = I.circ.cons + (2U * lo + lo1);
+    }
     fidK = nCons == 0 ? kNone : nCons - 1;
     const uint32_t fa = ldg(I.circ.firstAfter + l);
     const uint32_t avail = I.circ.nTwoQ - fa;

@@ -141,6 +141,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     cv.g1 = fG1.data();
     cv.consOff = fConsOff.data();
     cv.cons = fCons.data();
+    cv.consCnt = nullptr;
     cv.twoQ = fTwoQ.data();
     cv.firstAfter = fFirst.data();
     cv.nTwoQ = slot.nTwoQ;
