@@ -107,48 +107,87 @@ def host_cores() -> int:
 
 # ---------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region: NVML polled
+    every few ms from a thread (nvidia-smi in a loop as a fallback)."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap"}
+
     def __init__(self, index: int):
-        self.rows = []
-        self.proc = None
         self.index = index
+        self.rows = []  # (sm_mhz, max_mhz, reasons bitmask)
+        self.proc = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+
+    def _poll_nvml(self):
+        nv = self._nvml
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        while not self._stop.is_set():
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                self.rows.append((sm, mx, rs))
+            except Exception:
+                break
+            time.sleep(0.004)
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self._thread.start()
+            return
+        except Exception:
+            self._nvml = None
+        try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}",
-                 "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-                 "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "--query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+                 "clocks_event_reasons.hw_thermal_slowdown,"
                  "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+            self._thread = threading.Thread(target=self._read_smi, daemon=True)
+            self._thread.start()
         except OSError:
             self.proc = None
 
-    def _read(self):
+    def _read_smi(self):
+        bits = [0x8, 0x40, 0x20, 0x4]
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            r = [x.strip() for x in line.split(",")]
+            try:
+                rs = sum(b for b, v in zip(bits, r[2:6]) if v.lower().startswith("active"))
+                self.rows.append((float(r[0]), float(r[1]), rs))
+            except (ValueError, IndexError):
+                continue
 
     def stop(self):
+        self._stop.set()
         if self.proc is not None:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=2)
             except subprocess.TimeoutExpired:
                 self.proc.kill()
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+        sm = [r[0] for r in self.rows]
+        mx = max((r[1] for r in self.rows), default=0.0)
+        mask = 0
         for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx = max(mx, float(r[1]))
-            except (ValueError, IndexError):
-                continue
-            for nm, v in zip(names, r[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
+            mask |= r[2]
+        reasons = sorted(nm for bit, nm in self.REASONS.items() if mask & bit)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm)}
 
 
 def algorithmic_bytes(n: int, expanded: int, generated: int) -> float:
