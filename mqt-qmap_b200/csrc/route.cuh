@@ -15,7 +15,10 @@ namespace qmg {
 
 constexpr int kWarpsPerCta = 4;
 #ifndef QMG_MIN_CTAS
-#define QMG_MIN_CTAS 8
+// 6 CTAs (24 warps, 80 registers/thread) per SM measured best on config 2:
+// 3/4/5/6/8 -> 102/153/166/172/166 M nodes/s (the grid still holds 8 CTAs per
+// SM; the surplus CTAs start as earlier ones drain)
+#define QMG_MIN_CTAS 6
 #endif
 
 // upper bound of the per-warp working set (4 warps of a CTA must fit the

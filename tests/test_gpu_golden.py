@@ -158,3 +158,60 @@ def test_mapper_mirror_on_cuda():
     res = m.map(layering="disjoint_qubits", automatic_layer_splits_node_limit=3)
     assert res.layer_splits > 0
     assert mapper.verify_mapping(circ, m) == ""
+
+
+class _RawLayers:
+    """qmg_layers built by hand (what a C caller may pass): not necessarily the
+    product of createLayers."""
+
+    def __init__(self, n_logical, layers2, layers1):
+        import ctypes as C
+        self.off2 = np.zeros(len(layers2) + 1, dtype=np.uint32)
+        self.off1 = np.zeros(len(layers2) + 1, dtype=np.uint32)
+        g2, g1 = [], []
+        for l, (a, b) in enumerate(zip(layers2, layers1)):
+            g2 += a
+            g1 += b
+            self.off2[l + 1] = len(g2)
+            self.off1[l + 1] = len(g1)
+        self.g2 = np.array(g2, dtype=np.uint16).reshape(-1, 4)
+        self.g1 = np.array(g1, dtype=np.uint16).reshape(-1, 2)
+        v = _abi.QmgLayers()
+        v.n_layers = len(layers2)
+        v.n_logical = n_logical
+        v.gate2q_offsets = self.off2.ctypes.data
+        v.gates2q = self.g2.ctypes.data if len(self.g2) else None
+        v.gate1q_offsets = self.off1.ctypes.data
+        v.gates1q = self.g1.ctypes.data if len(self.g1) else None
+        self.layers = v
+        self.n_layers = len(layers2)
+
+
+def test_hand_made_layers_ragged_and_empty():
+    """layers a C caller may hand over: empty layers, layers whose gates share a
+    qubit, only-1q layers, an instance with no layers at all - the tables the
+    device derives from them give the oracle's results"""
+    from oracle import oracleapi
+    L = _abi.load()
+    a = arch_for("ibmq_tokyo")
+    n = a.n_qubits
+    oa = oracleapi.OracleArch(n, a.edges)
+    raw = _RawLayers(
+        8,
+        [[], [[0, 5, 1, 0], [5, 7, 0, 2]], [], [[1, 6, 1, 1]], [[0, 7, 2, 0], [2, 3, 1, 0], [4, 6, 0, 1]],
+         [], [[3, 5, 1, 0]]],
+        [[[2, 1]], [], [], [[1, 2], [3, 1], [4, 1]], [], [[0, 3]], []])
+    empty = _RawLayers(4, [], [])
+    for kw in (dict(), dict(heuristic=2, lookahead_heuristic="gate_count_sum_distance"),
+               dict(heuristic=3, initial_layout="identity", automatic_layer_splits=False)):
+        cfg = routing.make_config(debug=True, **kw)
+        init = np.arange(n, dtype=np.int16) if cfg.initial_layout == 0 else None
+        items = [routing.RouteItem(raw, init), routing.RouteItem(empty, init),
+                 routing.RouteItem(raw, init, 1)]
+        got = routing.route_batch(routing.CudaBackend(L, a.handle), n, cfg, items,
+                                  want_layer_qubits=True)
+        want = routing.route_batch(oracleapi.OracleBackend(oa), n, cfg, items,
+                                   want_layer_qubits=True)
+        for g, w in zip(got, want):
+            assert parity.compare_outputs(g, w) == "", kw
+        assert got[1].n_layers_done == 0 and got[1].status == 0
