@@ -250,7 +250,15 @@ typedef struct {
    * (n_route_layers = 0 means "to the end"); used to resume after a split */
   uint32_t first_layer;
   uint32_t n_route_layers;
-  uint32_t _pad;
+  /* capacity, in layers, of the per-layer outputs (layers, layer_qubits,
+   * layer_n_swaps); 0 = layers.n_layers.  With a capacity above n_layers the
+   * library splits layers itself when a search reaches
+   * automatic_layer_splits_node_limit (Mapper::splitLayer, src/sc/Mapper.cpp:
+   * 302-435, and the restart on the uncleared open list,
+   * HeuristicMapper.cpp:563-584), in pseudo-routing passes too; a circuit never
+   * ends up with more layers than it has (distinct) gate entries.  Otherwise a
+   * split is handed to the caller as QMG_SPLIT_LIMIT_HIT. */
+  uint32_t layer_capacity;
 } qmg_instance;
 
 /* result of one aStarMap call (HeuristicMapper::Node + the counters of
@@ -311,6 +319,13 @@ typedef struct {
    * layer of the final pass (n_layers entries).  With layers == NULL this is
    * all a caller needs to emit the routed circuit (routeCircuit :369-384). */
   uint16_t* layer_n_swaps;
+  /* layers split by the library in the final pass, in the order of the splits:
+   * entry k is the index (at that moment) of the layer that became layers
+   * index, index+1.  Replaying qmg_circuit_split_layer over this list gives the
+   * layer structure the per-layer outputs refer to (n_layers_done layers). */
+  uint32_t* split_layers; /* capacity split_capacity, or NULL */
+  uint32_t split_capacity;
+  uint32_t n_splits;
 } qmg_route_result;
 
 typedef struct {

@@ -21,13 +21,16 @@ struct qmg_batch {
   size_t nInst = 0;
   int n = 0;
   bool wantLayers = false, wantLayerQ = false, wantLayerNS = false;
-  std::vector<uint32_t> nLayers, swapCap;
-  std::vector<uint64_t> layerOff, swapOff;
-  uint64_t totLayers = 0, totSwapCap = 0;
+  // nLayers: layers of the instance's circuit; layerCap: rows of its
+  // per-layer outputs (more when the device may split layers)
+  std::vector<uint32_t> nLayers, layerCap, swapCap;
+  std::vector<uint64_t> layerOff, swapOff, splitOff;
+  uint64_t totLayers = 0, totSwapCap = 0, totSplitCap = 0;
+  bool deviceSplits = false;
   std::unique_ptr<qmg_workspace> ws;
   // output arena offsets (bytes)
   size_t oSummary = 0, oCounters = 0, oFinalQ = 0, oFinalL = 0, oStartL = 0,
-         oPlaces = 0, oSmallEnd = 0, oLayerNS = 0, oLayers = 0, oLayerQ = 0,
+         oPlaces = 0, oSplitLog = 0, oSmallEnd = 0, oLayerNS = 0, oLayers = 0, oLayerQ = 0,
          oSwapsPacked = 0, oSwapsWork = 0, oSwapCounter = 0, outSize = 0;
   // input arena offsets of what the launch needs
   size_t iInst = 0, iOrder = 0, iMem = 0, iTicket = 0, inSize = 0;
@@ -197,15 +200,21 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   sc.mark("dedupe");
   // ---- per-instance sizes
   b->nLayers.resize(nInst);
+  b->layerCap.resize(nInst);
+  b->splitOff.resize(nInst);
   b->layerOff.resize(nInst);
   b->swapCap.resize(nInst);
   b->swapOff.resize(nInst);
   for (size_t i = 0; i < nInst; ++i) {
     const auto& c = circs[circOf[i]];
     b->nLayers[i] = c.nLayers;
+    b->layerCap[i] = std::max(c.nLayers, instances[i].layer_capacity);
+    b->deviceSplits = b->deviceSplits || b->layerCap[i] > c.nLayers;
     b->layerOff[i] = b->totLayers;
-    b->totLayers += c.nLayers;
-    uint32_t cap = 4U * c.nLayers + 256U;
+    b->totLayers += b->layerCap[i];
+    b->splitOff[i] = b->totSplitCap;
+    b->totSplitCap += b->layerCap[i] - c.nLayers;
+    uint32_t cap = 4U * b->layerCap[i] + 256U;
     if (capacities != nullptr) {
       if (capacities[i].swaps != nullptr) {
         cap = capacities[i].swap_capacity;
@@ -244,7 +253,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   }
   uint32_t warpsPerSm = (opt != nullptr && opt->searches_per_sm != 0)
                             ? opt->searches_per_sm
-                            : 32U;
+                            : static_cast<uint32_t>(QMG_MIN_CTAS) * kWarpsPerCta;
+  // more than the register file admits would only queue idle CTAs
+  warpsPerSm = std::min<uint32_t>(
+      warpsPerSm, static_cast<uint32_t>(QMG_MIN_CTAS) * kWarpsPerCta);
   warpsPerSm = std::max<uint32_t>(kWarpsPerCta,
                                   warpsPerSm / kWarpsPerCta * kWarpsPerCta);
   while (warpsPerSm > kWarpsPerCta &&
@@ -312,6 +324,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->oFinalL = lo.add(nInst * n * 2);
   b->oStartL = lo.add(nInst * n * 2);
   b->oPlaces = lo.add(nInst * n * 4);
+  b->oSplitLog = lo.add(b->totSplitCap * 4);
   b->oSmallEnd = lo.size;
   b->oLayerNS = lo.add(b->wantLayerNS ? b->totLayers * 2 : 0);
   b->oLayers = lo.add(b->wantLayers ? b->totLayers * sizeof(LayerOut) : 0);
@@ -419,6 +432,25 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     maxG = std::max(maxG, c.maxG);
   }
   const size_t wNsw = lw.add(static_cast<size_t>(nWarps) * 32 * maxG * 2);
+  // private, writable circuit tables of every resident search (layers split
+  // on the device); too large a batch falls back to QMG_SPLIT_LIMIT_HIT
+  uint32_t privLayers = 0, privG2 = 0, privG1 = 0;
+  size_t privStride = 0, wPriv = 0;
+  if (b->deviceSplits) {
+    for (size_t i = 0; i < nInst; ++i) {
+      privLayers = std::max(privLayers, b->layerCap[i]);
+    }
+    for (const auto& c : circs) {
+      privG2 = std::max<uint32_t>(privG2, static_cast<uint32_t>(c.nG2) + 1U);
+      privG1 = std::max<uint32_t>(privG1, static_cast<uint32_t>(c.nG1) + 1U);
+    }
+    privStride = (privBytes(privLayers, privG2, privG1) + 255U) & ~size_t{255};
+    if (privStride * nWarps > (4ULL << 30)) {
+      b->deviceSplits = false;
+    } else {
+      wPriv = lw.add(privStride * nWarps);
+    }
+  }
   CU(W.work.ensure(lw.size));
   uint8_t* Wk = W.work.p;
   uint8_t* O = W.out.p;
@@ -467,6 +499,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.passes = instances[i].bidirectional_passes;
     I.firstLayer = instances[i].first_layer;
     I.nRoute = instances[i].n_route_layers;
+    I.layerCap = b->layerCap[i];
+    I.splitCap = b->layerCap[i] - c.nLayers;
+    I.splitLog = at<uint32_t>(O, b->oSplitLog) + b->splitOff[i];
     I.layers = b->wantLayers ? at<LayerOut>(O, b->oLayers) + b->layerOff[i]
                              : nullptr;
     I.layerNSwaps = b->wantLayerNS ? at<uint16_t>(O, b->oLayerNS) + b->layerOff[i]
@@ -513,6 +548,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     SearchMem* mem = at<SearchMem>(H, b->iMem);
     for (uint32_t w = 0; w < nWarps; ++w) {
       SearchMem& M = mem[w];
+      M = SearchMem{};
       M.pool = Wk + wPool + static_cast<size_t>(w) * poolNodes * recBytes;
       M.open = at<OpenEntry>(Wk, wOpen) + static_cast<size_t>(w) * poolNodes;
       M.table = at<uint64_t>(Wk, wTable) + static_cast<size_t>(w) * tableSize;
@@ -522,6 +558,12 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       M.tableMask = tableSize - 1;
       M.stamp = 0;
       M.maxG = maxG;
+      if (b->deviceSplits) {
+        M.priv = Wk + wPriv + static_cast<size_t>(w) * privStride;
+        M.privLayers = privLayers;
+        M.privG2 = privG2;
+        M.privG1 = privG1;
+      }
     }
   }
   sc.mark("views");
@@ -643,12 +685,20 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
     r.n_swaps_total = summary[8 * i];
     r.n_placements_total = summary[8 * i + 1];
     r.n_layers_done = summary[8 * i + 2];
+    r.n_splits = summary[8 * i + 5];
+    if (r.split_layers != nullptr) {
+      const uint32_t k = std::min(
+          {r.n_splits, r.split_capacity, b->layerCap[i] - b->nLayers[i]});
+      std::memcpy(r.split_layers, at<uint32_t>(Hh, b->oSplitLog) + b->splitOff[i],
+                  static_cast<size_t>(k) * 4);
+    }
     r.status = static_cast<int32_t>(summary[8 * i + 3]);
     r.expanded_nodes = counters[2 * i];
     r.generated_nodes = counters[2 * i + 1];
     exp.fetch_add(r.expanded_nodes, std::memory_order_relaxed);
     gen.fetch_add(r.generated_nodes, std::memory_order_relaxed);
-    const size_t nl = b->nLayers[i];
+    const size_t nl = std::min(
+        b->layerCap[i], std::max(b->nLayers[i], r.n_layers_done));
     if (r.layers != nullptr && b->wantLayers) {
       std::memcpy(r.layers, at<LayerOut>(Hh, b->oLayers) + b->layerOff[i],
                   nl * sizeof(LayerOut));

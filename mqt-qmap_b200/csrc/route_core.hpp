@@ -31,7 +31,9 @@
 #else
 #define QMG_HD_RED QMG_HD
 #endif
+#define QMG_COLD __host__ __device__ __noinline__
 #else
+#define QMG_COLD inline
 #define QMG_HD_RED inline
 #define QMG_HD inline
 #define QMG_D inline
@@ -133,6 +135,11 @@ struct InstView {
   const int16_t* initLoc;  // n or null
   uint32_t passes;         // bidirectional pseudo-routing passes
   uint32_t firstLayer, nRoute;
+  // capacity (in layers) of the per-layer outputs; layers split on the device
+  // (Mapper::splitLayer) need layerCap > circ.nLayers
+  uint32_t layerCap;
+  uint32_t splitCap;
+  uint32_t* splitLog;  // layer index of every split of the final pass, in order
   // outputs
   LayerOut* layers;
   uint16_t* swaps;
@@ -149,7 +156,8 @@ struct InstView {
   uint16_t* swapsPacked;
   uint32_t* swapCounter;
   // [0]=nSwapsTotal [1]=nPlaceTotal [2]=nLayersDone [3]=status
-  // [4]=offset of the instance's SWAPs in swapsPacked
+  // [4]=offset of the instance's SWAPs in swapsPacked [5]=layer splits of the
+  // final pass
   uint32_t* summary;
   uint64_t* counters;  // [0]=expanded [1]=generated (all passes)
 };
@@ -162,7 +170,14 @@ struct NodeHdr {  // 72 bytes, followed by qubits[n], locations[n]
   uint16_t swA, swB;
   uint16_t nValid, flags;  // flags bit0 valid, bit1 open
   uint32_t openPos;
-  uint32_t id, pad;
+  uint32_t id;
+  // a node that outlives a layer split (the restarted call inherits the open
+  // list) was scored against the unsplit layer: epoch = number of splits
+  // before the node was made; extra = entries of the reference's
+  // validMappedTwoQubitGates set that belong to gates no longer in the layer
+  // (children copy the set and only update gates of the current layer,
+  // HeuristicMapper.cpp:729-748, 861-973)
+  uint16_t epoch, extra;
 };
 static_assert(sizeof(NodeHdr) == 72, "NodeHdr layout");
 
@@ -191,6 +206,12 @@ struct SearchMem {
   uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
   uint32_t poolCap, recBytes, tableMask, stamp;
   uint32_t maxG;
+  // private, writable copy of the instance's circuit tables (layers split on
+  // the device); null = the device never splits
+  uint32_t privLayers, privG2, privG1;
+  uint8_t* priv;
+  uint32_t epoch;       // splits of the layer being searched so far
+  uint32_t childExtra;  // NodeHdr::extra of the children being generated
 };
 
 // per resident search, in shared memory (device) / one byte buffer (host).
@@ -308,9 +329,12 @@ template <class T> QMG_HD T ldg(const T* p) {
   return *p;
 #endif
 }
+// circuit tables are read with plain (coherent) loads: they may be the
+// search's private copy, which the search rewrites when it splits a layer
+template <class T> QMG_HD T ldc(const T* p) { return *p; }
 QMG_HD Gate2 ldGate(const Gate2* p) {
 #if defined(__CUDA_ARCH__)
-  const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+  const uint2 v = *reinterpret_cast<const uint2*>(p);
   Gate2 g;
   g.q1 = static_cast<uint16_t>(v.x & 0xffffU);
   g.q2 = static_cast<uint16_t>(v.x >> 16);
@@ -338,7 +362,7 @@ QMG_HD int popc32(uint32_t v) {
 }
 QMG_HD Gate1 ldGate1(const Gate1* p) {
 #if defined(__CUDA_ARCH__)
-  const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p));
+  const uint32_t v = *reinterpret_cast<const uint32_t*>(p);
   Gate1 g;
   g.q = static_cast<uint16_t>(v & 0xffffU);
   g.mult = static_cast<uint16_t>(v >> 16);
@@ -403,6 +427,258 @@ QMG_HD void gargmin(const Group& g, double& v, uint32_t& i) {
 }
 
 // ---------------------------------------------------------------------------
+// per-layer derived tables and layer splits
+// ---------------------------------------------------------------------------
+// getConsideredQubits(l) (HeuristicMapper.hpp:228-233: the qubits of the 2q
+// gates; of all gates for the fidelity-aware heuristic), ascending and unique,
+// written at cons + 2*g2Off[l] + g1Off[l]; Mapper::isLayerSplittable
+// (src/sc/Mapper.cpp:283-300).  Executed by ONE thread.
+QMG_HD void deriveLayerTables(const uint32_t* g2Off, const Gate2* g2,
+                              const uint32_t* g1Off, const Gate1* g1,
+                              uint16_t* cons, uint16_t* consCnt,
+                              uint8_t* splittable, uint32_t l, bool fidAware) {
+  const uint32_t a = g2Off[l], b = g2Off[l + 1];
+  const uint32_t a1 = g1Off[l], b1 = g1Off[l + 1];
+  uint16_t* out = cons + (2U * a + a1);
+  uint32_t cnt = 0;
+  // sorted insertion without duplicates (the lists are a handful long)
+  auto put = [&](uint16_t q) {
+    uint32_t k = 0;
+    while (k < cnt && out[k] < q) {
+      ++k;
+    }
+    if (k < cnt && out[k] == q) {
+      return;
+    }
+    for (uint32_t m = cnt; m > k; --m) {
+      out[m] = out[m - 1];
+    }
+    out[k] = q;
+    ++cnt;
+  };
+  for (uint32_t i = a; i < b; ++i) {
+    const Gate2 e = g2[i];
+    put(e.q1);
+    put(e.q2);
+  }
+  const uint32_t G = b - a, n1 = b1 - a1;
+  bool split = G > 1 || n1 > 2;
+  if (!split && G == 1) {
+    for (uint32_t i = a1; i < b1; ++i) {
+      const uint16_t q = g1[i].q;
+      bool in2 = false;
+      for (uint32_t k = 0; k < cnt; ++k) {
+        in2 = in2 || out[k] == q;
+      }
+      split = split || !in2;
+    }
+  }
+  if (fidAware) {
+    for (uint32_t i = a1; i < b1; ++i) {
+      put(g1[i].q);
+    }
+  }
+  consCnt[l] = static_cast<uint16_t>(cnt);
+  splittable[l] = split ? 1 : 0;
+}
+
+// the writable copy of one instance's circuit tables, carved from
+// SearchMem::priv for capacities (layers, 2q gate entries, 1q gate entries)
+struct PrivView {
+  uint32_t* active;  // != 0 while the search reads the private copy
+  CircView* saved;   // the shared view, to restore after the pass
+  uint32_t *g2Off, *g1Off, *twoQ, *firstAfter;
+  Gate2 *g2, *tmp2;
+  Gate1 *g1, *tmp1;
+  uint16_t *cons, *consCnt;
+  uint8_t* splittable;
+  uint32_t* ranges;  // [2e], [2e+1]: 2q gate range of the layer at epoch e
+  size_t bytes;
+};
+constexpr uint32_t kMaxEpochs = 64;
+QMG_HD PrivView privView(uint8_t* base, uint32_t capL, uint32_t capG2,
+                         uint32_t capG1) {
+  PrivView v;
+  size_t o = 0;
+  auto take = [&](size_t bytes) {
+    uint8_t* p = base + o;
+    o += (bytes + 15U) & ~static_cast<size_t>(15U);
+    return p;
+  };
+  v.active = reinterpret_cast<uint32_t*>(take(16));
+  v.saved = reinterpret_cast<CircView*>(take(sizeof(CircView)));
+  v.g2Off = reinterpret_cast<uint32_t*>(take(4U * (capL + 2U)));
+  v.g1Off = reinterpret_cast<uint32_t*>(take(4U * (capL + 2U)));
+  v.twoQ = reinterpret_cast<uint32_t*>(take(4U * (capL + 1U)));
+  v.firstAfter = reinterpret_cast<uint32_t*>(take(4U * (capL + 1U)));
+  v.g2 = reinterpret_cast<Gate2*>(take(sizeof(Gate2) * capG2));
+  v.tmp2 = reinterpret_cast<Gate2*>(take(sizeof(Gate2) * capG2));
+  v.g1 = reinterpret_cast<Gate1*>(take(sizeof(Gate1) * capG1));
+  v.tmp1 = reinterpret_cast<Gate1*>(take(sizeof(Gate1) * capG1));
+  v.cons = reinterpret_cast<uint16_t*>(take(2U * (2U * capG2 + capG1)));
+  v.consCnt = reinterpret_cast<uint16_t*>(take(2U * (capL + 1U)));
+  v.splittable = take(capL + 1U);
+  v.ranges = reinterpret_cast<uint32_t*>(take(8U * kMaxEpochs));
+  v.bytes = o;
+  return v;
+}
+
+inline size_t privBytes(uint32_t capL, uint32_t capG2, uint32_t capG1) {
+  // (only the offsets are wanted: any aligned address will do)
+  return privView(reinterpret_cast<uint8_t*>(static_cast<uintptr_t>(4096)), capL,
+                  capG2, capG1)
+      .bytes;
+}
+
+// switch the search to a private copy of its circuit tables
+QMG_COLD void privActivate(CircView* cv, uint8_t* priv, uint32_t capL,
+                           uint32_t capG2, uint32_t capG1, Group g) {
+  const PrivView p = privView(priv, capL, capG2, capG1);
+  const uint32_t nL = cv->nLayers;
+  const uint32_t nG2 = cv->g2Off[nL], nG1 = cv->g1Off[nL];
+  for (uint32_t i = g.lane; i <= nL; i += Group::W) {
+    p.g2Off[i] = cv->g2Off[i];
+    p.g1Off[i] = cv->g1Off[i];
+  }
+  for (uint32_t i = g.lane; i < nL; i += Group::W) {
+    p.firstAfter[i] = cv->firstAfter[i];
+    p.consCnt[i] = cv->consCnt[i];
+    p.splittable[i] = cv->splittable[i];
+  }
+  for (uint32_t i = g.lane; i < cv->nTwoQ; i += Group::W) {
+    p.twoQ[i] = cv->twoQ[i];
+  }
+  for (uint32_t i = g.lane; i < nG2; i += Group::W) {
+    p.g2[i] = cv->g2[i];
+  }
+  for (uint32_t i = g.lane; i < nG1; i += Group::W) {
+    p.g1[i] = cv->g1[i];
+  }
+  for (uint32_t i = g.lane; i < 2U * nG2 + nG1; i += Group::W) {
+    p.cons[i] = cv->cons[i];
+  }
+  g.sync();
+  if (g.lane == 0) {
+    *p.saved = *cv;
+    cv->g2Off = p.g2Off;
+    cv->g1Off = p.g1Off;
+    cv->g2 = p.g2;
+    cv->g1 = p.g1;
+    cv->cons = p.cons;
+    cv->consCnt = p.consCnt;
+    cv->twoQ = p.twoQ;
+    cv->firstAfter = p.firstAfter;
+    cv->splittable = p.splittable;
+    *p.active = 1;
+  }
+  g.sync();
+}
+
+// back to the shared tables (pseudoRouteCircuit restores the layers it split,
+// HeuristicMapper.cpp:309-344)
+QMG_COLD void privRestore(CircView* cv, uint8_t* priv, uint32_t capL,
+                          uint32_t capG2, uint32_t capG1, Group g) {
+  const PrivView p = privView(priv, capL, capG2, capG1);
+  g.sync();
+  if (g.lane == 0) {
+    *cv = *p.saved;
+    *p.active = 0;
+  }
+  g.sync();
+}
+
+// Mapper::splitLayer (src/sc/Mapper.cpp:302-435) on the private copy: layer l
+// keeps every second 2q gate (the 2nd, 4th, ...), the others move to a new
+// layer l+1; a 1q gate follows the 2q gate on its qubit, the remaining ones
+// alternate (first one stays).  Rare (once per splitLimit expansions at most),
+// so one lane does it.
+QMG_COLD void privSplit(CircView* cv, uint8_t* priv, uint32_t capL,
+                        uint32_t capG2, uint32_t capG1, uint32_t l,
+                        bool fidAware, Group g) {
+  const PrivView p = privView(priv, capL, capG2, capG1);
+  g.sync();
+  if (g.lane == 0) {
+    const uint32_t nL = cv->nLayers;
+    const uint32_t lo = p.g2Off[l], hi = p.g2Off[l + 1];
+    const uint32_t lo1 = p.g1Off[l], hi1 = p.g1Off[l + 1];
+    const uint32_t G = hi - lo, G1 = hi1 - lo1;
+    const uint32_t nKeep = G / 2U;
+    for (uint32_t i = 0; i < G; ++i) {
+      p.tmp2[i] = p.g2[lo + i];
+    }
+    for (uint32_t i = 0; i < G; ++i) {
+      const uint32_t dst = (i & 1U) != 0 ? i / 2U : nKeep + i / 2U;
+      p.g2[lo + dst] = p.tmp2[i];
+    }
+    // side of every 1q gate: 0 stays, 1 moves (kept in the layer's cons
+    // region, which is rebuilt below)
+    uint16_t* side = p.cons + (2U * lo + lo1);
+    bool stay = true;
+    uint32_t nKeep1 = 0;
+    for (uint32_t i = 0; i < G1; ++i) {
+      p.tmp1[i] = p.g1[lo1 + i];
+      const uint16_t q = p.tmp1[i].q;
+      bool inKeep = false, inMoved = false;
+      for (uint32_t k = 0; k < G; ++k) {
+        const bool hit = p.tmp2[k].q1 == q || p.tmp2[k].q2 == q;
+        if ((k & 1U) != 0) {
+          inKeep = inKeep || hit;
+        } else {
+          inMoved = inMoved || hit;
+        }
+      }
+      bool toKeep;
+      if (inKeep) {
+        toKeep = true;
+      } else if (inMoved) {
+        toKeep = false;
+      } else {
+        toKeep = stay;
+        stay = !stay;
+      }
+      side[i] = toKeep ? 0 : 1;
+      nKeep1 += toKeep ? 1U : 0U;
+    }
+    uint32_t k0 = 0, k1 = 0;
+    for (uint32_t i = 0; i < G1; ++i) {
+      if (side[i] == 0) {
+        p.g1[lo1 + k0++] = p.tmp1[i];
+      } else {
+        p.g1[lo1 + nKeep1 + k1++] = p.tmp1[i];
+      }
+    }
+    // insert layer l+1
+    for (uint32_t k = nL; k > l; --k) {
+      p.g2Off[k + 1] = p.g2Off[k];
+      p.g1Off[k + 1] = p.g1Off[k];
+    }
+    p.g2Off[l + 1] = lo + nKeep;
+    p.g1Off[l + 1] = lo1 + nKeep1;
+    for (uint32_t k = nL; k > l + 1; --k) {
+      p.consCnt[k] = p.consCnt[k - 1];
+      p.splittable[k] = p.splittable[k - 1];
+    }
+    deriveLayerTables(p.g2Off, p.g2, p.g1Off, p.g1, p.cons, p.consCnt,
+                      p.splittable, l, fidAware);
+    deriveLayerTables(p.g2Off, p.g2, p.g1Off, p.g1, p.cons, p.consCnt,
+                      p.splittable, l + 1, fidAware);
+    // Mapper::getNextLayer (Mapper.cpp:437-448) in closed form
+    uint32_t t = 0;
+    for (uint32_t k = 0; k <= nL; ++k) {
+      const bool has = p.g2Off[k + 1] > p.g2Off[k];
+      if (has) {
+        p.twoQ[t] = k;
+        ++t;
+      }
+      p.firstAfter[k] = t;
+    }
+    cv->nTwoQ = t;
+    cv->nLayers = nL + 1;
+  }
+  g.sync();
+}
+
+// ---------------------------------------------------------------------------
 // the search of one instance
 // ---------------------------------------------------------------------------
 // H = qmg_heuristic (0..4): one kernel instantiation per heuristic keeps the
@@ -413,7 +689,7 @@ template <int H> struct Search {
   static constexpr bool kTight = !kFid;  // isTight, Heuristic.hpp:96-110
   const ArchView& A;
   const CfgView& C;
-  const InstView& I;
+  InstView& I;  // (the circuit view is re-pointed when a layer is split)
   SearchMem& M;
   Scratch& S;
   Group g;
@@ -435,9 +711,10 @@ template <int H> struct Search {
   int16_t* pL = nullptr;
   bool tableMode = false;
   bool maskReady = false;
+  bool allowSplit = false;  // this aStarMap call may stop at the split limit
   uint64_t totExpanded = 0, totGenerated = 0;
 
-  QMG_HD Search(const ArchView& a, const CfgView& c, const InstView& i,
+  QMG_HD Search(const ArchView& a, const CfgView& c, InstView& i,
                 SearchMem& m, Scratch& s)
       : A(a), C(c), I(i), M(m), S(s), n(a.n) {}
 
@@ -598,7 +875,7 @@ template <int H> struct Search {
     const bool wantMax = (h == 0 || h == 3);
     const bool wantSum = (h == 1);
     const bool wantShared = (h == 2 || h == 3);
-    uint32_t nValid = 0;
+    uint32_t nValid = root ? 0U : M.childExtra;
     uint32_t revFixed = 0;  // recalculateFixedCostReversals :771-796
     double hMax = 0.;
     double hSum = 0.;
@@ -628,6 +905,10 @@ template <int H> struct Search {
           if (wantSum) {
             hSum += r;
           }
+        } else {
+          // only read when stale entries make the set as large as the layer
+          // although this gate is not adjacent (:771-796 then charges it)
+          revFixed += e.fwd * kCostReverse;
         }
       }
       if (wantShared && A.unidirectional) {
@@ -744,8 +1025,8 @@ template <int H> struct Search {
   // layer and one child layout.  Executed by ONE lane.
   QMG_HD double lookaheadPenalty(uint32_t ll, int a, int b, int q1,
                                  int q2) const {
-    const uint32_t lo = ldg(I.circ.g2Off + ll);
-    const uint32_t hi = ldg(I.circ.g2Off + ll + 1);
+    const uint32_t lo = ldc(I.circ.g2Off + ll);
+    const uint32_t hi = ldc(I.circ.g2Off + ll + 1);
     const bool isMax = (C.lookahead == 1);
     double penalty = 0.;
     QMG_NOUNROLL
@@ -812,7 +1093,7 @@ template <int H> struct Search {
           // in layer order below)
           S.lookPen()[it] =
               ldg(C.factors + s0 + sl) *
-              lookaheadPenalty(ldg(lookLayers + s0 + sl), a, b, q1, q2);
+              lookaheadPenalty(ldc(lookLayers + s0 + sl), a, b, q1, q2);
         }
         g.sync();
         QMG_NOUNROLL
@@ -852,7 +1133,7 @@ template <int H> struct Search {
         fixed += e.mult * ldg(A.c1 + pL[e.q]);
       }
     }
-    uint32_t nValid = 0;
+    uint32_t nValid = root ? 0U : M.childExtra;
     QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
@@ -1133,7 +1414,8 @@ template <int H> struct Search {
       h->flags = static_cast<uint16_t>((ch.valid ? 1U : 0U) | 2U);
       h->openPos = openPos;
       h->id = id;
-      h->pad = 0;
+      h->epoch = static_cast<uint16_t>(M.epoch);
+      h->extra = static_cast<uint16_t>(root ? 0U : M.childExtra);
     }
   }
 
@@ -1343,7 +1625,7 @@ template <int H> struct Search {
     int cnt = 0;
     QMG_NOUNROLL
     while (enumCi < nCons) {
-      const int q = ldg(cons + enumCi);
+      const int q = ldc(cons + enumCi);
       const int p = pL[q];
       const uint32_t lo = p < 0 ? 0U : ldg(A.incOff + p);
       const uint32_t hi = p < 0 ? 0U : ldg(A.incOff + p + 1);
@@ -1542,22 +1824,22 @@ template <int H> struct Search {
 
   QMG_HD void setLayer(uint32_t l) {
     layer = l;
-    const uint32_t lo = ldg(I.circ.g2Off + l);
-    G = ldg(I.circ.g2Off + l + 1) - lo;
+    const uint32_t lo = ldc(I.circ.g2Off + l);
+    G = ldc(I.circ.g2Off + l + 1) - lo;
     gates = I.circ.g2 + lo;
-    const uint32_t lo1 = ldg(I.circ.g1Off + l);
-    G1 = ldg(I.circ.g1Off + l + 1) - lo1;
+    const uint32_t lo1 = ldc(I.circ.g1Off + l);
+    G1 = ldc(I.circ.g1Off + l + 1) - lo1;
     gates1 = I.circ.g1 + lo1;
     if (I.circ.consOff != nullptr) {
-      const uint32_t loc = ldg(I.circ.consOff + l);
-      nCons = ldg(I.circ.consOff + l + 1) - loc;
+      const uint32_t loc = ldc(I.circ.consOff + l);
+      nCons = ldc(I.circ.consOff + l + 1) - loc;
       cons = I.circ.cons + loc;
     } else {
-      nCons = ldg(I.circ.consCnt + l);
+      nCons = ldc(I.circ.consCnt + l);
       cons = I.circ.cons + (2U * lo + lo1);
     }
     fidK = nCons == 0 ? kNone : nCons - 1;
-    const uint32_t fa = ldg(I.circ.firstAfter + l);
+    const uint32_t fa = ldc(I.circ.firstAfter + l);
     const uint32_t avail = I.circ.nTwoQ - fa;
     nLook = C.lookahead == 0 ? 0U
                              : (avail < C.nFactors ? avail : C.nFactors);
@@ -1576,7 +1858,7 @@ template <int H> struct Search {
     if (g.lane == 0) {
       QMG_NOUNROLL
       for (uint32_t i = 0; i < nCons; ++i) {
-        const int q = ldg(cons + i);
+        const int q = ldc(cons + i);
         S.consMask()[q >> 5] |= 1U << (q & 31);
       }
     }
@@ -1584,21 +1866,38 @@ template <int H> struct Search {
     g.sync();
   }
 
-  QMG_HD int astar(LayerStats& st) {
-    nPool = 0;
-    nOpen = 0;
+  // resume: the call restarts on a layer that was just split and inherits the
+  // open list of the interrupted call (:575-583 - `nodes` is not cleared)
+  QMG_HD int astar(LayerStats& st, bool resume) {
     nextId = 0;
-    tableMode = false;
     g.sync();
-    if (g.lane == 0) {
-      ++M.stamp;  // (M lives in shared memory on the device)
+    if (!resume) {
+      nPool = 0;
+      nOpen = 0;
+      tableMode = false;
+      if (g.lane == 0) {
+        ++M.stamp;  // (M lives in shared memory on the device)
+        M.epoch = 0;
+      }
+    } else if (g.lane == 0) {
+      M.epoch = M.epoch + 1 < kMaxEpochs ? M.epoch + 1 : kMaxEpochs - 1;
     }
     g.sync();
-    // layers are only split in the final pass (the host splits and resumes;
-    // a pseudo-routing pass searches on - the reference would split there too
-    // and undo it afterwards, :309-344)
+    if (g.lane == 0) {
+      M.childExtra = 0;
+      if (M.priv != nullptr) {
+        uint32_t* r =
+            privView(M.priv, M.privLayers, M.privG2, M.privG1).ranges + 2U * M.epoch;
+        r[0] = static_cast<uint32_t>(gates - I.circ.g2);
+        r[1] = r[0] + G;
+      }
+    }
+    g.sync();
+    // without a private circuit copy (SearchMem::priv) layers are only split
+    // in the final pass, by the host, which then resumes; a pseudo-routing
+    // pass searches on
     const bool splittable =
-        record && C.autoSplit != 0 && ldg(I.circ.splittable + layer) != 0;
+        allowSplit && C.autoSplit != 0 && ldc(I.circ.splittable + layer) != 0;
     // one loop iteration = evaluate one chunk of nodes (first the root from
     // the mapper's current layout, then the children of the node being
     // expanded) and push them; when a parent is exhausted the next node is
@@ -1626,7 +1925,7 @@ template <int H> struct Search {
         evaluate(cnt, rootMode, pc, parentHash);
         bool goalRoot = false;
         if (rootMode) {
-          goalRoot = S.ch()[0].valid != 0 && kTight;
+          goalRoot = S.ch()[0].valid != 0 && kTight && !resume;
         }
         if (!goalRoot || rootLookWanted) {
           scoreLookahead(cnt, rootMode);
@@ -1744,6 +2043,16 @@ template <int H> struct Search {
       }
       pc.fixed = h->fixed;
       pc.shared = h->shared;
+      {
+        uint32_t ex = h->extra;
+        if (h->epoch != M.epoch) {
+          ex += staleExtra(cur, h->epoch);
+        }
+        g.sync();
+        if (g.lane == 0) {
+          M.childExtra = ex;
+        }
+      }
       parentHash = h->hash;
       depth = h->depth + 1;
       parent = cur;
@@ -1760,12 +2069,58 @@ template <int H> struct Search {
 
 
   // one aStarMap call incl. mapUnmappedGates; adopts the result layout
-  QMG_HD int routeLayer(uint32_t l, bool finalPass, uint32_t& swapTotal) {
+  // node idx was made ep splits ago: the gates its layer had then and the
+  // current one has not, adjacent in the node's layout (these stay in the
+  // validMappedTwoQubitGates set its children copy)
+  QMG_HD uint32_t staleExtra(uint32_t idx, uint32_t ep) const {
+    const uint32_t* r =
+        privView(M.priv, M.privLayers, M.privG2, M.privG1).ranges + 2U * ep;
+    const uint32_t lo = r[0], hi = r[1];
+    const uint32_t cl = static_cast<uint32_t>(gates - I.circ.g2), ch = cl + G;
+    const int16_t* nl = nodeL(idx);
+    uint64_t cnt = 0;
+    QMG_NOUNROLL
+    for (uint32_t i = lo + g.lane; i < hi; i += Group::W) {
+      if (i < cl || i >= ch) {
+        const Gate2 e = ldGate(I.circ.g2 + i);
+        cnt += adjU(nl[e.q1], nl[e.q2]) ? 1U : 0U;
+      }
+    }
+    return static_cast<uint32_t>(gsum64(g, cnt));
+  }
+
+  // Mapper::splitLayer for the layer being searched
+  QMG_HD void splitOnDevice(uint32_t l, bool finalPass) {
+    const PrivView p = privView(M.priv, M.privLayers, M.privG2, M.privG1);
+    if (*p.active == 0) {
+      privActivate(&I.circ, M.priv, M.privLayers, M.privG2, M.privG1, g);
+    }
+    privSplit(&I.circ, M.priv, M.privLayers, M.privG2, M.privG1, l, kFid, g);
+    if (finalPass && g.lane == 0) {
+      const uint32_t k = I.summary[5];
+      if (I.splitLog != nullptr && k < I.splitCap) {
+        I.splitLog[k] = l;
+      }
+      I.summary[5] = k + 1;
+    }
+    g.sync();
+  }
+  QMG_HD void restoreSharedCircuit() {
+    if (M.priv != nullptr) {
+      const PrivView p = privView(M.priv, M.privLayers, M.privG2, M.privG1);
+      if (*p.active != 0) {
+        privRestore(&I.circ, M.priv, M.privLayers, M.privG2, M.privG1, g);
+      }
+    }
+  }
+
+  QMG_HD int routeLayer(uint32_t l, bool finalPass, bool reverse,
+                        uint32_t& swapTotal) {
     const bool wantRec = finalPass && I.layers != nullptr;
     if (!kFid && !wantRec) {
       // a layer without 2q gates needs no search when no record of it is
       // wanted: nothing to place, the root (1 generated node) is the result
-      if (ldg(I.circ.g2Off + l + 1) == ldg(I.circ.g2Off + l)) {
+      if (ldc(I.circ.g2Off + l + 1) == ldc(I.circ.g2Off + l)) {
         totGenerated += 1;
         if (finalPass) {
           if (I.layerNSwaps != nullptr && g.lane == 0) {
@@ -1788,7 +2143,35 @@ template <int H> struct Search {
       return ST_BAD_ARG;
     }
     LayerStats st;
-    const int rc = astar(st);
+    int rc;
+    bool resume = false;
+    QMG_NOUNROLL
+    for (;;) {
+      uint32_t room = 0;
+      if (M.priv != nullptr) {
+        room = M.privLayers;
+        if (finalPass && I.layerCap < room) {
+          room = I.layerCap;
+        }
+      }
+      const bool devSplit = I.circ.nLayers < room;
+      allowSplit = finalPass || devSplit;
+      st = LayerStats{};
+      rc = astar(st, resume);
+      if (rc != ST_SPLIT || !devSplit) {
+        break;
+      }
+      // the interrupted call leaves no trace in the counters (:575-583)
+      splitOnDevice(l, finalPass);
+      if (reverse) {
+        ++l;
+      }
+      setLayer(l);
+      if (!mapUnmappedGates()) {
+        return ST_BAD_ARG;
+      }
+      resume = true;
+    }
     totExpanded += st.expanded;
     totGenerated += nextId;
     if (rc != ST_OK) {
@@ -1900,11 +2283,16 @@ template <int H> struct Search {
 
   // HeuristicMapper::map :74-91 for one instance
   QMG_HD void run() {
-    const uint32_t nL = I.circ.nLayers;
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       S.curQ()[i] = -1;
       S.curL()[i] = -1;
+    }
+    if (g.lane == 0) {
+      I.summary[5] = 0;
+      if (M.priv != nullptr) {
+        *privView(M.priv, M.privLayers, M.privG2, M.privG1).active = 0;
+      }
     }
     g.sync();
     if (I.initLoc != nullptr) {
@@ -1923,14 +2311,18 @@ template <int H> struct Search {
     uint32_t doneLayers = 0;
     QMG_NOUNROLL
     for (uint32_t pass = 0; pass < I.passes && rc == ST_OK; ++pass) {
+      // (the layer count grows when a layer is split; every pseudo-routing
+      // pass ends by restoring the layers, :309-344)
       QMG_NOUNROLL
-      for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
-        rc = routeLayer(i, false, swapTotal);
+      for (uint32_t i = 0; i < I.circ.nLayers && rc == ST_OK; ++i) {
+        rc = routeLayer(i, false, false, swapTotal);
       }
+      restoreSharedCircuit();
       QMG_NOUNROLL
-      for (uint32_t i = 0; i < nL && rc == ST_OK; ++i) {
-        rc = routeLayer(nL - 1 - i, false, swapTotal);
+      for (uint32_t i = 0; i < I.circ.nLayers && rc == ST_OK; ++i) {
+        rc = routeLayer(I.circ.nLayers - 1 - i, false, true, swapTotal);
       }
+      restoreSharedCircuit();
     }
     if (rc == ST_OK) {
       if (I.startL != nullptr) {
@@ -1940,17 +2332,22 @@ template <int H> struct Search {
         }
       }
       const uint32_t first = I.firstLayer;
-      const uint32_t last =
-          (I.nRoute == 0 || first + I.nRoute > nL) ? nL : first + I.nRoute;
       doneLayers = first;
       QMG_NOUNROLL
-      for (uint32_t l = first; l < last; ++l) {
-        rc = routeLayer(l, true, swapTotal);
+      for (uint32_t l = first;; ++l) {
+        const uint32_t nL = I.circ.nLayers;
+        const uint32_t last =
+            (I.nRoute == 0 || first + I.nRoute > nL) ? nL : first + I.nRoute;
+        if (l >= last) {
+          break;
+        }
+        rc = routeLayer(l, true, false, swapTotal);
         if (rc != ST_OK) {
           break;
         }
         ++doneLayers;
       }
+      restoreSharedCircuit();
     }
     g.sync();
     QMG_NOUNROLL

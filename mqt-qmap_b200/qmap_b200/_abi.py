@@ -70,7 +70,7 @@ class QmgInstance(C.Structure):
     _fields_ = [
         ("layers", QmgLayers), ("initial_locations", C.c_void_p),
         ("bidirectional_passes", C.c_uint32), ("first_layer", C.c_uint32),
-        ("n_route_layers", C.c_uint32), ("_pad", C.c_uint32),
+        ("n_route_layers", C.c_uint32), ("layer_capacity", C.c_uint32),
     ]
 
 
@@ -85,6 +85,8 @@ class QmgRouteResult(C.Structure):
         ("n_layers_done", C.c_uint32), ("status", C.c_int32),
         ("expanded_nodes", C.c_uint64), ("generated_nodes", C.c_uint64),
         ("layer_n_swaps", C.c_void_p),
+        ("split_layers", C.c_void_p), ("split_capacity", C.c_uint32),
+        ("n_splits", C.c_uint32),
     ]
 
 

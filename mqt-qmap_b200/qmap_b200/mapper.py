@@ -18,6 +18,10 @@ from ._abi import QmapError
 from .circuit import Circuit, Op
 
 
+class InvalidPlacement(QmapError):
+    """a routed layer leaves a two-qubit gate on qubits that are not coupled"""
+
+
 @dataclass
 class MappingResults:
     """The fields of MappingResults (include/sc/MappingResults.hpp) this path
@@ -32,6 +36,7 @@ class MappingResults:
     output_cnots: int = 0
     output_single_qubit_gates: int = 0
     layer_splits: int = 0
+    rerouted_with_host_splits: bool = False
     expanded_nodes: int = 0
     generated_nodes: int = 0
     time: float = 0.0
@@ -98,9 +103,27 @@ class HeuristicMapper:
 
     # ------------------------------------------------------------------
     def map(self, config=None, **kwargs) -> MappingResults:
-        """HeuristicMapper::map (:44-107)."""
+        """HeuristicMapper::map (:44-107).
+
+        Layer splits are first left to the library, which follows the
+        reference bit for bit (restart on the uncleared open list).  That
+        restart can return a node whose validMappedTwoQubitGates set still
+        counts gates of the unsplit layer, i.e. a "valid" layout in which a
+        gate of the layer is not adjacent; the reference then only asserts
+        (:414) and a release build emits a CNOT on a non-edge.  Such a result
+        is detected at emission and the circuit is routed again with the
+        layers split on this side and a fresh open list per restart, which is
+        always valid (MappingResults.rerouted_with_host_splits)."""
         cfg = config if config is not None else routing.make_config(**kwargs)
         self._check_parameters(cfg)
+        try:
+            return self._map_once(cfg, True)
+        except InvalidPlacement:
+            res = self._map_once(cfg, False)
+            res.rerouted_with_host_splits = True
+            return res
+
+    def _map_once(self, cfg, library_splits: bool) -> MappingResults:
         t_start = time.perf_counter()
         n = self.architecture.n_qubits
         c, t, identity = self.qc.mapper_view(n)
@@ -120,9 +143,15 @@ class HeuristicMapper:
             init = None
         start_given = init.copy() if init is not None else np.full(n, -1, dtype=np.int16)
 
-        # ---- route; a layer that hits the split limit is split on the host
-        # and the search resumes from that layer with the layout reached so far
+        # ---- route.  The per-layer outputs get room for every layer a split can
+        # add (a circuit never has more layers than gates), so the library
+        # splits layers itself like the reference (restart on the uncleared
+        # open list, splits in pseudo-routing passes) and reports the splits of
+        # the final pass.  Should it still hand a split back
+        # (QMG_SPLIT_LIMIT_HIT), the layer is split here and the search resumes
+        # from it with the layout reached so far.
         backend = self._backend_or_default()
+        extra = len(c) if cfg.automatic_layer_splits and library_splits else 0
         passes = int(cfg.iterative_bidirectional_routing_passes)
         first = 0
         lq_parts, ns_parts, swap_parts, place_parts = [], [], [], []
@@ -130,7 +159,11 @@ class HeuristicMapper:
         splits = 0
         while True:
             item = routing.RouteItem(lc, init, passes, first_layer=first)
-            out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True, lean=True)[0]
+            out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True, lean=True,
+                                      extra_layers=extra)[0]
+            if out.split_layers is not None and len(out.split_layers):
+                lc = lc.split_copy(out.split_layers)
+                splits += len(out.split_layers)
             if start_locations is None:
                 start_locations = out.start_locations.copy()
             done = out.n_layers_done
@@ -229,7 +262,7 @@ class HeuristicMapper:
                     pc, pt = int(locations[c[g]]), int(locations[t[g]])
                     if (pc, pt) not in directed:
                         if (pt, pc) not in directed:
-                            raise QmapError("invalid CNOT placement in the routed circuit")
+                            raise InvalidPlacement("invalid CNOT placement in the routed circuit")
                         for q in (pt, pc):
                             out_ops.append(Op("h", (q,)))
                         out_ops.append(Op(op.name, (pt, pc), op.params))

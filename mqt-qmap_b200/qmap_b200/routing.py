@@ -94,12 +94,14 @@ class LayeredCircuit:
             self.lib.qmg_circuit_destroy(self.h)
             self.h = None
 
-    def split_copy(self, layer: int) -> "LayeredCircuit":
+    def split_copy(self, layer) -> "LayeredCircuit":
         """A new circuit with the same gates and split history plus a split of
-        `layer` (Mapper::splitLayer); this object is left untouched, other
+        `layer` (Mapper::splitLayer; a sequence = several splits in that order,
+        e.g. RouteOutput.split_layers); this object is left untouched, other
         routing instances may share it."""
         out = LayeredCircuit(self.lib, self.n, self.control, self.target, self.layering)
-        for l in self.splits + [int(layer)]:
+        more = [int(layer)] if np.isscalar(layer) else [int(l) for l in layer]
+        for l in self.splits + more:
             out.split(l)
         return out
 
@@ -156,6 +158,7 @@ class RouteOutput:
     start_locations: np.ndarray
     layer_qubits: np.ndarray | None = None
     layer_n_swaps: np.ndarray | None = None  # uint16 per layer
+    split_layers: np.ndarray | None = None  # layers split by the backend (final pass)
     _offsets: np.ndarray | None = None
 
     def layer_swaps(self, layer: int) -> np.ndarray:
@@ -184,13 +187,16 @@ class BatchBuffers:
     lns: list = field(default_factory=list)
     keep: list = field(default_factory=list)
     layer_cap: list = field(default_factory=list)  # per-instance rows of layers/lq/lns
+    split_logs: list = field(default_factory=list)
 
 
 def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False,
          extra_layers=0) -> BatchBuffers:
     """lean: no per-layer qmg_layer_result records, only the compact per-layer
     SWAP counts (what circuit emission needs).  extra_layers: additional rows
-    in the per-layer outputs for backends that split layers themselves."""
+    in the per-layer outputs; with extra_layers > 0 the backend splits layers
+    itself (qmg_instance.layer_capacity) and reports the splits of the final
+    pass in RouteOutput.split_layers."""
     nI = len(items)
     b = BatchBuffers(n=n, items=list(items))
     b.inst = (QmgInstance * nI)()
@@ -213,6 +219,12 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False,
         ins.bidirectional_passes = it.bidirectional_passes
         ins.first_layer = it.first_layer
         ins.n_route_layers = it.n_route_layers
+        if extra_layers > 0:
+            ins.layer_capacity = cap_l
+            slog = np.zeros(extra_layers, dtype=np.uint32)
+            b.split_logs.append(slog)
+            b.res[i].split_layers = slog.ctypes.data
+            b.res[i].split_capacity = extra_layers
         cap = swap_capacity if swap_capacity is not None else 4 * cap_l + 256
         lr = None if lean else np.zeros(cap_l, dtype=LAYER_RESULT_DTYPE)
         sw = np.zeros((max(cap, 1), 2), dtype=np.uint16)
@@ -254,7 +266,9 @@ def unpack(b: BatchBuffers) -> list:
             swaps=b.swaps[i][: min(int(r.n_swaps_total), len(b.swaps[i]))],
             placements=b.places[i][: int(r.n_placements_total)],
             final_qubits=b.fq[i], final_locations=b.fl[i], start_locations=b.sl[i],
-            layer_qubits=b.lq[i][:nl] if b.lq else None))
+            layer_qubits=b.lq[i][:nl] if b.lq else None,
+            split_layers=(b.split_logs[i][: min(int(r.n_splits), len(b.split_logs[i]))]
+                          if b.split_logs else None)))
     return outs
 
 

@@ -411,6 +411,7 @@ struct Router {
   std::vector<Edge> placedNow;
   uint64_t expandedAll = 0, generatedAll = 0;
   uint32_t splits = 0;
+  std::vector<uint32_t> splitLog;  // layers split in the final pass, in order
 
   Router(const Arch& a, const qmg_config& c) : A(a), cfg(c) {
     // HeuristicMapper::map :51-52, Heuristic.hpp:96-125
@@ -487,6 +488,9 @@ struct Router {
     layers[l] = keep;
     layers.insert(layers.begin() + static_cast<std::ptrdiff_t>(l) + 1, moved);
     ++splits;
+    if (record) {
+      splitLog.push_back(static_cast<uint32_t>(l));
+    }
   }
 
   // ---- placement of not yet mapped qubits -------------------------------
@@ -1265,6 +1269,12 @@ QO_API int qo_route(const qo_arch* h, const qmg_config* cfg,
   res->n_swaps_total = nSwaps;
   res->n_placements_total = nPlaced;
   res->n_layers_done = static_cast<uint32_t>(nL);
+  res->n_splits = static_cast<uint32_t>(r.splitLog.size());
+  for (size_t k = 0; k < r.splitLog.size(); ++k) {
+    if (res->split_layers != nullptr && k < res->split_capacity) {
+      res->split_layers[k] = r.splitLog[k];
+    }
+  }
   res->status = status;
   res->expanded_nodes = r.expandedAll;
   res->generated_nodes = r.generatedAll;

@@ -139,9 +139,18 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     cv.g2 = fG2.data();
     cv.g1Off = fG1Off.data();
     cv.g1 = fG1.data();
-    cv.consOff = fConsOff.data();
-    cv.cons = fCons.data();
-    cv.consCnt = nullptr;
+    // considered qubits / splittable flags in the layout the device derives
+    // (derive.cuh), by the same function
+    std::vector<uint16_t> dCons(2 * slot.nG2 + slot.nG1 + 1);
+    std::vector<uint16_t> dConsCnt(nLy + 1);
+    for (uint32_t l = 0; l < nLy; ++l) {
+      deriveLayerTables(fG2Off.data(), fG2.data(), fG1Off.data(), fG1.data(),
+                        dCons.data(), dConsCnt.data(), fSplit.data(), l,
+                        C.fidelityAware != 0);
+    }
+    cv.consOff = nullptr;
+    cv.cons = dCons.data();
+    cv.consCnt = dConsCnt.data();
     cv.twoQ = fTwoQ.data();
     cv.firstAfter = fFirst.data();
     cv.nTwoQ = slot.nTwoQ;
@@ -157,12 +166,25 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.tableMask = tableSize - 1;
     M.stamp = stamp;
     M.maxG = fc.maxG;
+    // device-side layer splits: a private, writable copy of the tables
+    const uint32_t layerCap = std::max<uint32_t>(in.layer_capacity, slot.nLayers);
+    std::vector<uint64_t> privStore;
+    if (layerCap > slot.nLayers) {
+      M.privLayers = layerCap;
+      M.privG2 = static_cast<uint32_t>(slot.nG2) + 1;
+      M.privG1 = static_cast<uint32_t>(slot.nG1) + 1;
+      privStore.resize(privBytes(M.privLayers, M.privG2, M.privG1) / 8 + 2);
+      M.priv = reinterpret_cast<uint8_t*>(privStore.data());
+    }
     InstView I{};
     I.circ = cv;
     I.initLoc = in.initial_locations;
     I.passes = in.bidirectional_passes;
     I.firstLayer = in.first_layer;
     I.nRoute = in.n_route_layers;
+    I.layerCap = layerCap;
+    I.splitLog = r.split_layers;
+    I.splitCap = r.split_layers != nullptr ? r.split_capacity : 0;
     I.layers = reinterpret_cast<LayerOut*>(r.layers);
     I.swaps = r.swaps;
     I.swapCap = r.swap_capacity;
@@ -188,6 +210,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     r.n_swaps_total = summary[0];
     r.n_placements_total = summary[1];
     r.n_layers_done = summary[2];
+    r.n_splits = summary[5];
     r.status = static_cast<int32_t>(summary[3]);
     r.expanded_nodes = counters[0];
     r.generated_nodes = counters[1];

@@ -222,13 +222,16 @@ def read_arch_file(name):
     return n, e.astype(np.uint16)
 
 
-def run_golden(backend, lib, n, g: GoldenRun, rel=0.0, layer_capacity_extra=0):
-    """Route the golden case `g` with `backend`; returns (msg, out)."""
+def run_golden(backend, lib, n, g: GoldenRun, rel=0.0, backend_splits=True, options=None):
+    """Route the golden case `g` with `backend`; returns (msg, out).  Cases in
+    which the reference split a layer get room for the split layers, which
+    makes the backend split layers itself (qmg_instance.layer_capacity)."""
     kw = dict(g.meta["config"])
     kw["debug"] = True
     cfg = routing.make_config(**kw)
     circ = qcirc.load_qasm(os.path.join(CIRCUITS, g.meta["circuit"]))
     out = routing.route_batch(backend, n, cfg, [item_for(lib, n, circ, cfg)],
-                              want_layer_qubits=True,
-                              extra_layers=max(0, g.n_layers - 0) if g.meta["split"] else 0)[0]
+                              want_layer_qubits=True, options=options,
+                              extra_layers=g.n_layers if g.meta["split"] and backend_splits
+                              else 0)[0]
     return compare(out, g, rel, allow_split=True), out

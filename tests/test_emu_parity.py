@@ -51,9 +51,31 @@ def test_split_request_is_reported():
     QMG_SPLIT_LIMIT_HIT and names the layer (the host splits and resumes)."""
     g = next(g for g in parity.golden_runs() if g.meta["split"] and g.generated_nodes < 5000)
     be = emu_for(g.meta["arch"], g.meta["calibration"])
-    msg, out = parity.run_golden(be, be.lib, be.n, g)
+    msg, out = parity.run_golden(be, be.lib, be.n, g, backend_splits=False)
     assert out.status == _abi.QMG_SPLIT_LIMIT_HIT
     assert out.n_layers_done < g.n_layers
+
+
+SPLIT_RUNS = [g for g in parity.golden_runs() if g.meta["split"] and g.generated_nodes <= 50000]
+
+
+def test_layer_splits_match_reference_outputs():
+    """Cases in which the reference split layers (final pass and pseudo-routing
+    passes): with room for the new layers the search splits them itself
+    (Mapper::splitLayer) and restarts on the uncleared open list like the
+    reference - every call agrees bit for bit, stale nodes included."""
+    assert len(SPLIT_RUNS) >= 28
+    bad, splits = [], 0
+    for g in SPLIT_RUNS:
+        be = emu_for(g.meta["arch"], g.meta["calibration"])
+        msg, out = parity.run_golden(be, be.lib, be.n, g)
+        if msg:
+            bad.append((g.label, msg))
+        else:
+            splits += len(out.split_layers)
+            assert out.n_layers_done == g.n_layers
+    assert not bad, bad[:3]
+    assert splits > 100
 
 
 def test_lean_outputs_match_full_records():
@@ -73,3 +95,39 @@ def test_lean_outputs_match_full_records():
     assert np.array_equal(lean.swaps, full.swaps)
     for l in (0, 5, len(full.layers) - 1):
         assert np.array_equal(lean.layer_swaps(l), full.layer_swaps(l))
+
+
+@pytest.mark.parametrize("arch,calib", [("ibm_qx5", None), ("ibmq_tokyo", None),
+                                        ("ibmq_london", "ibmq_london.csv")])
+def test_random_circuits_with_layer_splits_against_oracle(arch, calib):
+    """Seeded random circuits with tiny split limits: all five heuristics,
+    pseudo-routing passes in both directions (splits there are undone after
+    the pass), identity and dynamic layouts - records, SWAPs, layouts, the
+    split log and the node totals equal the CPU restatement's."""
+    from oracle import oracleapi
+    from qmap_b200 import circuit as qcirc
+    be = emu_for(arch, calib)
+    n, e = parity.read_arch_file(arch)
+    oa = oracleapi.OracleArch(n, e)
+    if calib:
+        oa.set_fidelity_costs(T[f"{arch}_c1"], T[f"{arch}_c2"], T[f"{arch}_cswap"])
+    ob = oracleapi.OracleBackend(oa)
+    splits = 0
+    for seed in range(20):
+        circ = qcirc.random_circuit(n - (seed % 3) if n > 6 else n, 20 + 2 * seed, seed=seed)
+        heur = seed % 5 if calib else seed % 4
+        cfg = routing.make_config(
+            heuristic=heur, layering=("disjoint_qubits", "disjoint_2q_blocks")[seed % 2],
+            initial_layout=("dynamic", "identity")[(seed // 2) % 2],
+            lookahead_heuristic="none" if heur == 4 else
+            ("gate_count_max_distance", "none", "gate_count_sum_distance")[seed % 3],
+            iterative_bidirectional_routing_passes=(seed // 3) % 2,
+            automatic_layer_splits_node_limit=(2, 3, 5, 9)[seed % 4], debug=True)
+        item = parity.item_for(be.lib, n, circ, cfg)
+        a = routing.route_batch(be, n, cfg, [item], want_layer_qubits=True, extra_layers=200)[0]
+        b = routing.route_batch(ob, n, cfg, [item], want_layer_qubits=True, extra_layers=200)[0]
+        assert parity.compare_outputs(a, b) == "", (arch, seed)
+        assert np.array_equal(a.split_layers, b.split_layers), (arch, seed)
+        assert (a.expanded_nodes, a.generated_nodes) == (b.expanded_nodes, b.generated_nodes)
+        splits += len(b.split_layers)
+    assert splits > 50

@@ -215,3 +215,82 @@ def test_hand_made_layers_ragged_and_empty():
         for g, w in zip(got, want):
             assert parity.compare_outputs(g, w) == "", kw
         assert got[1].n_layers_done == 0 and got[1].status == 0
+
+
+SPLIT_RUNS = [g for g in parity.golden_runs() if g.meta["split"]]
+
+
+def test_layer_splits_match_reference_outputs():
+    """every case in which the reference split a layer (final pass and pseudo-
+    routing passes): the kernel splits the layer itself (Mapper::splitLayer on
+    its private copy of the circuit tables) and restarts on the uncleared open
+    list - all calls agree bit for bit, the split log replays to the
+    reference's layer structure"""
+    assert len(SPLIT_RUNS) >= 30
+    L = _abi.load()
+    bad, splits = [], 0
+    for g in SPLIT_RUNS:
+        a = arch_for(g.meta["arch"], g.meta["calibration"])
+        be = routing.CudaBackend(L, a.handle)
+        opts = None
+        if g.generated_nodes > 100000:
+            opts = _abi.QmgRouteOptions()
+            opts.pool_nodes = 1 << 20
+        msg, out = parity.run_golden(be, L, a.n_qubits, g, options=opts)
+        if msg:
+            bad.append((g.label, msg))
+            continue
+        splits += len(out.split_layers)
+        cfg = routing.make_config(**g.meta["config"])
+        circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
+        lc = parity.item_for(L, a.n_qubits, circ, cfg).circuit
+        if len(out.split_layers):
+            lc = lc.split_copy(out.split_layers)
+        assert lc.n_layers == g.n_layers, g.label
+    assert not bad, bad[:3]
+    assert splits > 100
+
+
+def test_batch_with_layer_splits_against_oracle():
+    """one launch, many instances that split layers (seeded random circuits,
+    tiny split limits, pseudo-routing passes): lean outputs and split logs equal
+    the CPU restatement's, instance by instance"""
+    from oracle import oracleapi
+    L = _abi.load()
+    for arch, calib, heurs in (("ibm_qx5", None, (0, 1, 2, 3)), ("ibmq_tokyo", None, (0, 3)),
+                               ("ibmq_london", "ibmq_london.csv", (4,))):
+        a = arch_for(arch, calib)
+        n = a.n_qubits
+        oa = oracleapi.OracleArch(n, a.edges)
+        if calib:
+            t = parity.golden_tables()
+            oa.set_fidelity_costs(t[f"{arch}_c1"], t[f"{arch}_c2"], t[f"{arch}_cswap"])
+        for heur in heurs:
+            for passes in (0, 1):
+                cfg = routing.make_config(
+                    heuristic=heur, layering=("disjoint_qubits", "disjoint_2q_blocks")[heur % 2],
+                    lookahead_heuristic="none" if heur == 4 else "gate_count_max_distance",
+                    iterative_bidirectional_routing_passes=passes,
+                    automatic_layer_splits_node_limit=(2, 3, 5)[heur % 3])
+                items = []
+                for seed in range(24):
+                    circ = qcirc.random_circuit(n - (seed % 3) if n > 6 else n, 24 + 2 * seed,
+                                                seed=1000 * heur + seed)
+                    items.append(parity.item_for(L, n, circ, cfg))
+                got = routing.route_batch(routing.CudaBackend(L, a.handle), n, cfg, items * 3,
+                                          lean=True, extra_layers=160)
+                want = routing.route_batch(oracleapi.OracleBackend(oa), n, cfg, items,
+                                           lean=True, extra_layers=160)
+                nsplit = 0
+                for i, o in enumerate(got):
+                    w = want[i % len(items)]
+                    key = (arch, heur, passes, i)
+                    assert o.status == 0 and o.n_layers_done == w.n_layers_done, key
+                    assert np.array_equal(o.split_layers, w.split_layers), key
+                    assert np.array_equal(o.layer_n_swaps, w.layer_n_swaps), key
+                    assert np.array_equal(o.swaps, w.swaps), key
+                    assert np.array_equal(o.final_qubits, w.final_qubits), key
+                    assert (o.expanded_nodes, o.generated_nodes) == \
+                        (w.expanded_nodes, w.generated_nodes), key
+                    nsplit += len(w.split_layers)
+                assert nsplit > 0, (arch, heur, passes)

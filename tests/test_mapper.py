@@ -35,6 +35,7 @@ def test_mapped_circuits_verify_and_match_reference_swap_counts():
     assert len(CASES) > 60
     bad = []
     n_split = 0
+    n_rerouted = 0
     for g in CASES:
         a, be = arch_and_backend(g.meta["arch"])
         circ = qcirc.load_qasm(os.path.join(parity.CIRCUITS, g.meta["circuit"]))
@@ -45,18 +46,23 @@ def test_mapped_circuits_verify_and_match_reference_swap_counts():
             bad.append((g.label, msg))
             continue
         if g.meta["split"]:
+            # layers are split by the library exactly like the reference
+            # (pseudo-routing passes included): same final layer structure
             n_split += 1
-            # (pseudo-routing passes are not split by the product, so with
-            # bidirectional passes the reference may have split only there)
-            if res.layer_splits == 0 and not g.meta["config"].get(
-                    "iterative_bidirectional_routing_passes"):
-                bad.append((g.label, "reference split a layer, the mapper did not"))
-        elif res.output_swaps != g.swaps:
+            if res.rerouted_with_host_splits:
+                # the reference's own result for this case places a CNOT on
+                # qubits that are not coupled (see HeuristicMapper.map)
+                n_rerouted += 1
+                continue
+            if res.input_layers != g.n_layers:
+                bad.append((g.label, f"layers {res.input_layers} != {g.n_layers}"))
+        if res.output_swaps != g.swaps:
             # (swap_on_first_layer is off: the first layer's SWAPs fold into
             # the initial layout in both implementations)
             bad.append((g.label, f"swaps {res.output_swaps} != {g.swaps}"))
     assert not bad, bad[:5]
     assert n_split >= 5
+    assert n_rerouted <= 1
 
 
 def test_static_and_identity_layouts():
