@@ -82,6 +82,47 @@ def _ref_worker(args):
     return exp, gen, swaps, time.perf_counter() - t0, search_s
 
 
+def _ref_worker_c4(args):
+    seeds, n_cx, tmpdir = args
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "mqt-qmap_b200"))
+    from oracle import refapi
+    from qmap_b200 import workloads
+    R = refapi.Ref()
+    arch_path, csv_path = workloads.c4_files(os.path.join(tmpdir, f"w{os.getpid()}"))
+    ra = R.arch_load(arch_path, csv_path)  # (table build: not part of the timed search)
+    cfg = refapi.make_config(debug=True, **workloads.C4_CONFIG)
+    exp = gen = swaps = 0
+    search_s = 0.0
+    t0 = time.perf_counter()
+    for s in seeds:
+        c, t = workloads.c4_circuit(s, n_cx).gate_arrays()
+        rr = R.map_gates(ra, 127, c, t, cfg)
+        exp += rr.expanded_nodes
+        gen += rr.generated_nodes
+        swaps += rr.swaps
+        search_s += rr.seconds_per_node * rr.expanded_nodes
+    return exp, gen, swaps, time.perf_counter() - t0, search_s
+
+
+def run_reference_c4(seeds, cores: int, n_cx: int):
+    """Config 4 with the reference on `cores` processes; same return value as
+    run_reference."""
+    from concurrent.futures import ProcessPoolExecutor
+    import multiprocessing as mp
+    import tempfile
+    chunks = [list(seeds[i::cores]) for i in range(cores)]
+    chunks = [c for c in chunks if c]
+    tmpdir = tempfile.mkdtemp(prefix="qmap_c4_ref_")
+    t0 = time.perf_counter()
+    with ProcessPoolExecutor(max_workers=len(chunks), mp_context=mp.get_context("spawn")) as ex:
+        res = list(ex.map(_ref_worker_c4, [(c, n_cx, tmpdir) for c in chunks]))
+    wall = time.perf_counter() - t0
+    busy = max(r[3] for r in res)
+    return (sum(r[0] for r in res), sum(r[1] for r in res), sum(r[2] for r in res),
+            busy, wall, sum(r[4] for r in res))
+
+
 def run_reference(seeds, cores: int):
     """Routes the given instances with the reference on `cores` processes.
     Returns (expanded, generated, swaps, wall seconds)."""

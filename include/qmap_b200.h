@@ -336,6 +336,17 @@ typedef struct {
    * SWAP lists, layouts) instead of the full qmg_layer_result records; with
    * qmg_route_batch the result pointers decide */
   uint32_t lean_outputs;
+  /* cap on the resident searches of the whole grid (rounded down to whole
+   * CTAs of 4 searches), 0 = none.  Few searches with large node pools suit
+   * instances whose layers need millions of nodes. */
+  uint32_t max_searches;
+  /* Every search starts in a lean variant of the kernel (flat scan of the
+   * open list, no layer splits on the device) and the instance is routed
+   * again by the full variant when an open list outgrows 4096 nodes or a layer
+   * has to be split; results are identical either way.  1 = use the full
+   * variant from the start (long searches expected), 2 = lean first,
+   * 0 = auto (full for fidelity-aware routing on more than 32 qubits). */
+  uint32_t search_variant;
 } qmg_route_options;
 
 typedef struct {
@@ -349,7 +360,11 @@ typedef struct {
   uint64_t expanded_nodes; /* sum over instances and passes */
   uint64_t generated_nodes;
   uint32_t kernel_launches;
-  uint32_t _pad;
+  /* qmg_route_batch with pool_nodes == 0: instances whose node pool ran out
+   * and that were routed again with fewer resident searches and larger pools
+   * (up to three such rounds; an instance still failing keeps
+   * QMG_POOL_EXHAUSTED) */
+  uint32_t retried_instances;
 } qmg_route_stats;
 
 /*

@@ -36,6 +36,7 @@ struct qmg_batch {
   size_t iInst = 0, iOrder = 0, iMem = 0, iTicket = 0, inSize = 0;
   size_t tableOff = 0, tableBytes = 0;
   uint32_t grid = 0, poolNodes = 0;
+  uint32_t startFull = 0;  // route_kernel: full search variant from the start
   Scratch sl{};
   size_t smemBytes = 0;
   uint64_t h2dBytes = 0;
@@ -269,6 +270,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   const uint32_t needCtas = static_cast<uint32_t>(
       std::max<size_t>(1, (nInst + kWarpsPerCta - 1) / kWarpsPerCta));
   b->grid = std::min(maxCtas, needCtas);
+  if (opt != nullptr && opt->max_searches != 0) {
+    b->grid = std::max<uint32_t>(
+        1, std::min(b->grid, opt->max_searches / kWarpsPerCta));
+  }
   const uint32_t nWarps = b->grid * kWarpsPerCta;
   const uint32_t recBytes =
       static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
@@ -278,6 +283,14 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       size_t freeB = 0, totalB = 0;
       CU(cudaMemGetInfo(&freeB, &totalB));
       W.memBudget = std::min<size_t>(freeB / 2, 16ULL << 30);
+      // QMAP_B200_POOL_MB: the first-tier budget of the node pools (tests use
+      // it to make the pools run out)
+      if (const char* e = std::getenv("QMAP_B200_POOL_MB")) {
+        const long mb = std::atol(e);
+        if (mb > 0) {
+          W.memBudget = std::min<size_t>(freeB / 2, static_cast<size_t>(mb) << 20);
+        }
+      }
     }
     const size_t budget = W.memBudget;
     const size_t perNode = recBytes + sizeof(OpenEntry) + 4 * sizeof(uint64_t);
@@ -287,6 +300,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     poolNodes = static_cast<uint32_t>(pn);
   }
   b->poolNodes = poolNodes;
+  {
+    const uint32_t v = opt != nullptr ? opt->search_variant : 0U;
+    b->startFull = v == 1 || (v == 0 && cfg->heuristic >= 4 && n > 32) ? 1U : 0U;
+  }
   uint32_t tableSize = 1;
   while (tableSize < 2 * poolNodes) {
     tableSize <<= 1;
@@ -340,6 +357,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   const size_t wOpen =
       lw.add(static_cast<size_t>(nWarps) * poolNodes * sizeof(OpenEntry));
   const size_t wTable = lw.add(static_cast<size_t>(nWarps) * tableSize * 8);
+  const size_t btopPerWarp = poolNodes / kBlk + 2;
+  const size_t wBtop =
+      lw.add(static_cast<size_t>(nWarps) * btopPerWarp * sizeof(OpenEntry));
   b->tableOff = wTable;
   b->tableBytes = static_cast<size_t>(nWarps) * tableSize * 8;
 
@@ -552,6 +572,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       M.pool = Wk + wPool + static_cast<size_t>(w) * poolNodes * recBytes;
       M.open = at<OpenEntry>(Wk, wOpen) + static_cast<size_t>(w) * poolNodes;
       M.table = at<uint64_t>(Wk, wTable) + static_cast<size_t>(w) * tableSize;
+      M.btop = at<OpenEntry>(Wk, wBtop) + static_cast<size_t>(w) * btopPerWarp;
       M.nsw = at<uint16_t>(Wk, wNsw) + static_cast<size_t>(w) * 32 * maxG;
       M.poolCap = poolNodes;
       M.recBytes = recBytes;
@@ -617,7 +638,8 @@ int batchRun(qmg_batch* b, qmg_route_stats* stats) {
     uint32_t* ticket = at<uint32_t>(W.out.p, b->oSwapCounter) + 1;
 #define QMG_LAUNCH(HH)                                                         \
   route_kernel<HH><<<b->grid, blk, b->smemBytes, s>>>(av, b->cfg, inst, order, \
-                                                      nI, mem, ticket, b->sl)
+                                                      nI, mem, ticket, b->sl,  \
+                                                      b->startFull)
     switch (b->cfg.heuristic) {
     case 0:
       QMG_LAUNCH(0);
@@ -800,6 +822,88 @@ QMG_API int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
     if (int rc = batchRun(b, stats)) {
       return rc;
     }
-    return batchFetch(b, results, stats);
+    if (int rc = batchFetch(b, results, stats)) {
+      return rc;
+    }
+    if (options != nullptr && options->pool_nodes != 0) {
+      return static_cast<int>(QMG_OK);
+    }
+    // ---- instances whose node pool ran out: again, with fewer resident
+    // searches and pools 16 times as large, out of most of the free HBM
+    uint64_t pool = b->poolNodes;
+    const size_t perNode = ((sizeof(NodeHdr) + 4U * static_cast<size_t>(b->n) + 7U) & ~size_t{7}) +
+                           sizeof(OpenEntry) + 4 * sizeof(uint64_t) + 1;
+    bool retried = false;
+    for (int tier = 0; tier < 3; ++tier) {
+      std::vector<size_t> idx;
+      for (size_t i = 0; i < nInstances; ++i) {
+        if (results[i].status == QMG_POOL_EXHAUSTED) {
+          idx.push_back(i);
+        }
+      }
+      if (idx.empty()) {
+        break;
+      }
+      retried = true;
+      hold->ws->work.release();
+      hold.reset();
+      size_t freeB = 0, totalB = 0;
+      CU(cudaMemGetInfo(&freeB, &totalB));
+      const size_t budget = freeB / 10 * 8;
+      pool = std::min<uint64_t>(pool * 16, 1ULL << 26);
+      pool = std::min<uint64_t>(pool, budget / (kWarpsPerCta * perNode));
+      qmg_route_options o2{};
+      if (options != nullptr) {
+        o2 = *options;
+      }
+      o2.pool_nodes = static_cast<uint32_t>(pool);
+      o2.max_searches = static_cast<uint32_t>(std::max<size_t>(
+          kWarpsPerCta,
+          std::min<size_t>(budget / (pool * perNode), size_t{1} << 20)));
+      std::vector<qmg_instance> inst2(idx.size());
+      std::vector<qmg_route_result> res2(idx.size());
+      for (size_t j = 0; j < idx.size(); ++j) {
+        inst2[j] = instances[idx[j]];
+        res2[j] = results[idx[j]];
+      }
+      qmg_batch* b2 = nullptr;
+      if (int rc = batchCreate(arch, cfg, idx.size(), inst2.data(), &o2,
+                               res2.data(), &b2)) {
+        return rc;
+      }
+      hold.reset(b2);
+      qmg_route_stats st2{};
+      if (int rc = batchRun(b2, &st2)) {
+        return rc;
+      }
+      if (int rc = batchFetch(b2, res2.data(), &st2)) {
+        return rc;
+      }
+      for (size_t j = 0; j < idx.size(); ++j) {
+        results[idx[j]] = res2[j];
+      }
+      if (stats != nullptr) {
+        stats->kernel_ms += st2.kernel_ms;
+        stats->h2d_ms += st2.h2d_ms;
+        stats->d2h_ms += st2.d2h_ms;
+        stats->h2d_bytes += st2.h2d_bytes;
+        stats->d2h_bytes += st2.d2h_bytes;
+        stats->kernel_launches += st2.kernel_launches;
+        stats->retried_instances += static_cast<uint32_t>(idx.size());
+      }
+    }
+    if (retried) {
+      hold->ws->work.release();  // (most of the HBM: not kept between calls)
+      hold->ws->memBudget = 0;
+      if (stats != nullptr) {
+        stats->expanded_nodes = 0;
+        stats->generated_nodes = 0;
+        for (size_t i = 0; i < nInstances; ++i) {
+          stats->expanded_nodes += results[i].expanded_nodes;
+          stats->generated_nodes += results[i].generated_nodes;
+        }
+      }
+    }
+    return static_cast<int>(QMG_OK);
   });
 }

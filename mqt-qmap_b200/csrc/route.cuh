@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
     route_kernel(ArchView A, CfgView C, const InstView* __restrict__ inst,
                  const uint32_t* __restrict__ order, uint32_t nInst,
                  SearchMem* __restrict__ mem, uint32_t* __restrict__ ticket,
-                 Scratch lay) {
+                 Scratch lay, uint32_t startFull) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = static_cast<int>(threadIdx.x) >> 5;
   const int lane = static_cast<int>(threadIdx.x) & 31;
@@ -65,18 +65,20 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
       }
     }
     __syncwarp();
-#ifdef QMG_DESC_REGS
-    const InstView rI = *sI;
-    SearchMem rM = *sM;
-    Search<H> s(A, C, rI, rM, S);
-    s.run();
-    if (lane == 0) {
-      sM->stamp = rM.stamp;
+    // the lean variant first; an instance with a long open list or a layer
+    // to split is routed again, from its first layer, by the full variant
+    // (startFull: the host expects long searches, e.g. fidelity-aware routing
+    // on a large architecture)
+    bool full = startFull != 0;
+    if (!full) {
+      Search<H, false> s(A, C, *sI, *sM, S);
+      full = !s.run();
+      __syncwarp();
     }
-#else
-    Search<H> s(A, C, *sI, *sM, S);
-    s.run();
-#endif
+    if (full) {
+      Search<H, true> s(A, C, *sI, *sM, S);
+      s.run();
+    }
     __syncwarp();
   }
   if (lane == 0) {

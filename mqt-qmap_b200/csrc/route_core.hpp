@@ -52,11 +52,23 @@ constexpr int kLookBlock = 16; // lookahead layers scored per pass
 // lookahead scratch: a (kChunk/2) x kLookBlock block of terms
 constexpr int kLookPenDoubles = (kChunk / 2) * kLookBlock;
 constexpr uint32_t kScanMax = 96;  // open-list length up to which push() scans
+// open lists longer than kBlkMin keep the top of every kBlk-entry block, so
+// that a pop reads the block tops and re-scans one block instead of the list
+#ifndef QMG_BLK
+#define QMG_BLK 512
+#define QMG_BLK_MIN 4096
+#endif
+constexpr uint32_t kBlk = QMG_BLK;  // (tests build the host variant with 4 / 8)
+constexpr uint32_t kBlkMin = QMG_BLK_MIN;
 
 enum Status : int32_t {
   ST_OK = 0,
   ST_NO_VIABLE = 1,
   ST_SPLIT = 2,
+  // internal: the lean variant of the search met a long open list or a layer
+  // to split; the instance is routed again by the full variant (never
+  // reported to the caller)
+  ST_NEEDS_FULL = 100,
   ST_BAD_ARG = 3,
   ST_POOL = 6,
   ST_BUFFER = 8,
@@ -203,6 +215,9 @@ struct SearchMem {
   uint8_t* pool;
   OpenEntry* open;
   uint64_t* table;
+  // tops of the kBlk-entry blocks of `open` (kept once the open list is long,
+  // see Search::blkEnter): poolCap / kBlk + 2 entries
+  OpenEntry* btop;
   uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
   uint32_t poolCap, recBytes, tableMask, stamp;
   uint32_t maxG;
@@ -684,7 +699,14 @@ QMG_COLD void privSplit(CircView* cv, uint8_t* priv, uint32_t capL,
 // H = qmg_heuristic (0..4): one kernel instantiation per heuristic keeps the
 // resident code of a launch small (the instruction cache, not the data path,
 // bounds this kernel)
-template <int H> struct Search {
+// kFull = false is the variant the common case runs: open lists are scanned
+// flat and layers are never split on the device, which keeps its resident
+// code and register use small (the kernel is instruction-fetch bound).  It
+// gives up with ST_NEEDS_FULL as soon as an open list outgrows kBlkMin or a
+// layer has to be split; the caller then routes the instance again with
+// kFull = true (per-block tops of the open list, Mapper::splitLayer and the
+// restart on the stale open list).
+template <int H, bool kFull> struct Search {
   static constexpr bool kFid = (H == 4);
   static constexpr bool kTight = !kFid;  // isTight, Heuristic.hpp:96-110
   const ArchView& A;
@@ -710,6 +732,7 @@ template <int H> struct Search {
   int16_t* pQ = nullptr;  // layout the scoring functions read
   int16_t* pL = nullptr;
   bool tableMode = false;
+  bool blockMode = false;  // M.btop holds the top of every open-list block
   bool maskReady = false;
   bool allowSplit = false;  // this aStarMap call may stop at the split limit
   uint64_t totExpanded = 0, totGenerated = 0;
@@ -875,7 +898,7 @@ template <int H> struct Search {
     const bool wantMax = (h == 0 || h == 3);
     const bool wantSum = (h == 1);
     const bool wantShared = (h == 2 || h == 3);
-    uint32_t nValid = root ? 0U : M.childExtra;
+    uint32_t nValid = (root || !kFull) ? 0U : M.childExtra;
     uint32_t revFixed = 0;  // recalculateFixedCostReversals :771-796
     double hMax = 0.;
     double hSum = 0.;
@@ -1133,7 +1156,7 @@ template <int H> struct Search {
         fixed += e.mult * ldg(A.c1 + pL[e.q]);
       }
     }
-    uint32_t nValid = root ? 0U : M.childExtra;
+    uint32_t nValid = (root || !kFull) ? 0U : M.childExtra;
     QMG_NOUNROLL
     for (uint32_t i = 0; i < G; ++i) {
       const Gate2 e = ldGate(gates + i);
@@ -1261,9 +1284,26 @@ template <int H> struct Search {
     }
     return 0;
   }
+  // what the open-list order needs of the search, by value (the out-of-line
+  // helpers of long open lists must not take `this`: that would force the
+  // whole Search object into local memory)
+  struct OpenCtx {
+    const uint8_t* pool;
+    uint32_t recBytes;
+    int n;
+  };
+  QMG_HD OpenCtx octx() const { return OpenCtx{M.pool, M.recBytes, n}; }
+  QMG_HD static const int16_t* nodeQOf(const OpenCtx& c, uint32_t idx) {
+    return reinterpret_cast<const int16_t*>(
+        c.pool + static_cast<size_t>(idx) * c.recBytes + sizeof(NodeHdr));
+  }
+  QMG_HD static const NodeHdr* hdrOf(const OpenCtx& c, uint32_t idx) {
+    return reinterpret_cast<const NodeHdr*>(c.pool +
+                                            static_cast<size_t>(idx) * c.recBytes);
+  }
   // 4 consecutive qubits[] entries as one integer whose unsigned order is the
   // lexicographic order of the (signed) entries
-  QMG_HD uint64_t lexChunk(const int16_t* q, int i0) const {
+  QMG_HD static uint64_t lexChunkOf(int n, const int16_t* q, int i0) {
     uint64_t k = 0;
     for (int t = 0; t < 4; ++t) {
       const int i = i0 + t;
@@ -1275,27 +1315,34 @@ template <int H> struct Search {
     }
     return k;
   }
+  QMG_HD uint64_t lexChunk(const int16_t* q, int i0) const {
+    return lexChunkOf(n, q, i0);
+  }
   // full order incl. the lexicographic tie-break (:438-450, :482): among
   // tied nodes the lexicographically LARGEST qubits[] is on top
-  QMG_HD bool hasPriority(const OpenEntry& x, const OpenEntry& y) const {
-    const int c = cmp4(x, y);
-    if (c != 0) {
-      return c < 0;
+  QMG_HD static bool hasPriorityOf(const OpenCtx& c, const OpenEntry& x,
+                                   const OpenEntry& y) {
+    const int r = cmp4(x, y);
+    if (r != 0) {
+      return r < 0;
     }
     if (x.idx == y.idx) {
       return false;
     }
-    const int16_t* qx = nodeQ(x.idx);
-    const int16_t* qy = nodeQ(y.idx);
+    const int16_t* qx = nodeQOf(c, x.idx);
+    const int16_t* qy = nodeQOf(c, y.idx);
     QMG_NOUNROLL
-    for (int i = 0; i < n; i += 4) {
-      const uint64_t kx = lexChunk(qx, i);
-      const uint64_t ky = lexChunk(qy, i);
+    for (int i = 0; i < c.n; i += 4) {
+      const uint64_t kx = lexChunkOf(c.n, qx, i);
+      const uint64_t ky = lexChunkOf(c.n, qy, i);
       if (kx != ky) {
         return kx > ky;
       }
     }
     return false;
+  }
+  QMG_HD bool hasPriority(const OpenEntry& x, const OpenEntry& y) const {
+    return hasPriorityOf(octx(), x, y);
   }
 
   QMG_HD uint32_t gmaxU32(uint32_t v) const { return gmaxU32V(v); }
@@ -1306,7 +1353,10 @@ template <int H> struct Search {
   // then narrowed key by key (cost band, validity, heuristic band, valid-gate
   // count, lexicographic layout), which selects the same node as the pairwise
   // order whenever that order is a strict weak order.
-  QMG_HD uint32_t topPos() const {
+  QMG_HD static uint32_t topOfS(const OpenCtx& c, const OpenEntry* arr,
+                                uint32_t lo, uint32_t hi) {
+    const Group g;
+    const int n = c.n;
     OpenEntry best;
     uint32_t bestPos = kNone;
     best.f = DBL_MAX;
@@ -1316,9 +1366,9 @@ template <int H> struct Search {
     best.nValid = 0;
     best.valid = 0;
     QMG_NOUNROLL
-    for (uint32_t i = g.lane; i < nOpen; i += Group::W) {
-      const OpenEntry e = M.open[i];
-      if (bestPos == kNone || hasPriority(e, best)) {
+    for (uint32_t i = lo + g.lane; i < hi; i += Group::W) {
+      const OpenEntry e = arr[i];
+      if (bestPos == kNone || hasPriorityOf(c, e, best)) {
         best = e;
         bestPos = i;
       }
@@ -1337,14 +1387,14 @@ template <int H> struct Search {
       }
       const double hmn = gmin(g, cand ? best.h2 : DBL_MAX);
       cand = cand && !(fabs(best.h2 - hmn) > kTol);
-      const uint32_t nv = gmaxU32(cand ? best.nValid + 1U : 0U);
+      const uint32_t nv = gmaxU32V(cand ? best.nValid + 1U : 0U);
       cand = cand && (best.nValid + 1U == nv);
       m = g.ballot(cand);
-      const int16_t* q = cand ? nodeQ(best.idx) : nullptr;
+      const int16_t* q = cand ? nodeQOf(c, best.idx) : nullptr;
       QMG_NOUNROLL
       for (int i = 0; i < n && popc32(m) > 1; i += 4) {
-        const uint64_t k = cand ? lexChunk(q, i) : 0ULL;
-        const uint64_t kmx = gmaxU64(k);
+        const uint64_t k = cand ? lexChunkOf(n, q, i) : 0ULL;
+        const uint64_t kmx = gmaxU64V(k);
         cand = cand && k == kmx;
         m = g.ballot(cand);
       }
@@ -1353,9 +1403,89 @@ template <int H> struct Search {
     return g.bcast(bestPos, src);
   }
 
+  // ---- long open lists: tops per block (M.btop); out of line and static so
+  // that neither the resident code nor the registers of the short-list path
+  // change
+  QMG_COLD static uint32_t blkTopOf(OpenCtx c, const OpenEntry* arr, uint32_t lo,
+                                    uint32_t hi) {
+    return topOfS(c, arr, lo, hi);
+  }
+  QMG_COLD static void blkRescan(OpenCtx c, const OpenEntry* open,
+                                 OpenEntry* btop, uint32_t nOpen, uint32_t b) {
+    const Group g;
+    const uint32_t lo = b * kBlk;
+    const uint32_t hi = lo + kBlk < nOpen ? lo + kBlk : nOpen;
+    const uint32_t p = blkTopOf(c, open, lo, hi);
+    if (g.lane == 0) {
+      btop[b] = open[p];
+    }
+    g.sync();
+  }
+  QMG_COLD static void blkEnter(OpenCtx c, const OpenEntry* open, OpenEntry* btop,
+                                uint32_t nOpen) {
+    const Group g;
+    g.sync();
+    const uint32_t nb = (nOpen + kBlk - 1) / kBlk;
+    QMG_NOUNROLL
+    for (uint32_t b = 0; b < nb; ++b) {
+      blkRescan(c, open, btop, nOpen, b);
+    }
+  }
+  QMG_COLD static uint32_t blkTopPos(OpenCtx c, const OpenEntry* btop,
+                                     uint32_t nOpen) {
+    const uint32_t nb = (nOpen + kBlk - 1) / kBlk;
+    const uint32_t b = blkTopOf(c, btop, 0, nb);
+    return hdrOf(c, btop[b].idx)->openPos;
+  }
+  // the entry at pos was appended (fresh: it opened a new block) or replaced
+  // by a better one
+  QMG_COLD static void blkChanged(OpenCtx c, const OpenEntry* open,
+                                  OpenEntry* btop, uint32_t pos, bool fresh) {
+    const Group g;
+    if (g.lane == 0) {
+      const OpenEntry e = open[pos];
+      const uint32_t b = pos / kBlk;
+      bool take = fresh;
+      if (!take) {
+        const OpenEntry t = btop[b];
+        take = t.idx == e.idx || hasPriorityOf(c, e, t);
+      }
+      if (take) {
+        btop[b] = e;
+      }
+    }
+    g.sync();
+  }
+  // the entry at pos was removed and the one at `last` (= nOpen now) moved
+  // into its place
+  QMG_COLD static void blkRemoved(OpenCtx c, const OpenEntry* open,
+                                  OpenEntry* btop, uint32_t nOpen, uint32_t pos,
+                                  uint32_t movedIdx) {
+    const uint32_t last = nOpen;
+    const uint32_t bp = pos / kBlk;
+    const uint32_t bl = last / kBlk;
+    if (bp * kBlk < nOpen) {
+      blkRescan(c, open, btop, nOpen, bp);
+    }
+    if (bl != bp && bl * kBlk < nOpen && btop[bl].idx == movedIdx) {
+      blkRescan(c, open, btop, nOpen, bl);
+    }
+  }
+
+  QMG_HD uint32_t topPos() const {
+    if (kFull && blockMode) {
+      return blkTopPos(octx(), M.btop, nOpen);
+    }
+    return topOfS(octx(), M.open, 0, nOpen);
+  }
+
   QMG_HD void removeOpen(uint32_t pos) {
     // group-uniform; lane 0 writes
     const uint32_t last = nOpen - 1;
+    uint32_t moved = kNone;
+    if (kFull && blockMode) {
+      moved = M.open[last].idx;
+    }
     if (g.lane == 0) {
       const uint32_t idx = M.open[pos].idx;
       hdr(idx)->flags &= static_cast<uint16_t>(~2U);
@@ -1367,6 +1497,9 @@ template <int H> struct Search {
     }
     nOpen = last;
     g.sync();
+    if (kFull && blockMode) {
+      blkRemoved(octx(), M.open, M.btop, nOpen, pos, moved);
+    }
   }
 
   // write a node record: parent layout (pQ/pL) with the child's swap
@@ -1414,8 +1547,10 @@ template <int H> struct Search {
       h->flags = static_cast<uint16_t>((ch.valid ? 1U : 0U) | 2U);
       h->openPos = openPos;
       h->id = id;
-      h->epoch = static_cast<uint16_t>(M.epoch);
-      h->extra = static_cast<uint16_t>(root ? 0U : M.childExtra);
+      if (kFull) {
+        h->epoch = static_cast<uint16_t>(M.epoch);
+        h->extra = static_cast<uint16_t>(root ? 0U : M.childExtra);
+      }
     }
   }
 
@@ -1537,6 +1672,9 @@ template <int H> struct Search {
           M.open[pos] = ne;
         }
         g.sync();
+        if (kFull && blockMode) {
+          blkChanged(octx(), M.open, M.btop, pos, false);
+        }
       }
       return true;
     }
@@ -1553,6 +1691,9 @@ template <int H> struct Search {
       }
     }
     g.sync();
+    if (kFull && blockMode) {
+      blkChanged(octx(), M.open, M.btop, pos, pos % kBlk == 0);
+    }
     return true;
   }
 
@@ -1875,15 +2016,16 @@ template <int H> struct Search {
       nPool = 0;
       nOpen = 0;
       tableMode = false;
+      blockMode = false;
       if (g.lane == 0) {
         ++M.stamp;  // (M lives in shared memory on the device)
         M.epoch = 0;
       }
-    } else if (g.lane == 0) {
+    } else if (kFull && g.lane == 0) {
       M.epoch = M.epoch + 1 < kMaxEpochs ? M.epoch + 1 : kMaxEpochs - 1;
     }
     g.sync();
-    if (g.lane == 0) {
+    if (kFull && g.lane == 0) {
       M.childExtra = 0;
       if (M.priv != nullptr) {
         uint32_t* r =
@@ -2001,6 +2143,14 @@ template <int H> struct Search {
       if (nOpen == 0) {
         break;
       }
+      if (!kFull) {
+        if (nOpen > kBlkMin) {
+          return ST_NEEDS_FULL;
+        }
+      } else if (!blockMode && nOpen > kBlkMin) {
+        blkEnter(octx(), M.open, M.btop, nOpen);
+        blockMode = true;
+      }
       const uint32_t pos = topPos();
       const OpenEntry top = M.open[pos];
       if (found && !(top.f < bestFixedTotal)) {
@@ -2043,7 +2193,7 @@ template <int H> struct Search {
       }
       pc.fixed = h->fixed;
       pc.shared = h->shared;
-      {
+      if (kFull) {
         uint32_t ex = h->extra;
         if (h->epoch != M.epoch) {
           ex += staleExtra(cur, h->epoch);
@@ -2106,7 +2256,7 @@ template <int H> struct Search {
     g.sync();
   }
   QMG_HD void restoreSharedCircuit() {
-    if (M.priv != nullptr) {
+    if (kFull && M.priv != nullptr) {
       const PrivView p = privView(M.priv, M.privLayers, M.privG2, M.privG1);
       if (*p.active != 0) {
         privRestore(&I.circ, M.priv, M.privLayers, M.privG2, M.privG1, g);
@@ -2160,6 +2310,9 @@ template <int H> struct Search {
       rc = astar(st, resume);
       if (rc != ST_SPLIT || !devSplit) {
         break;
+      }
+      if (!kFull) {
+        return ST_NEEDS_FULL;
       }
       // the interrupted call leaves no trace in the counters (:575-583)
       splitOnDevice(l, finalPass);
@@ -2281,8 +2434,10 @@ template <int H> struct Search {
     return ST_OK;
   }
 
-  // HeuristicMapper::map :74-91 for one instance
-  QMG_HD void run() {
+  // HeuristicMapper::map :74-91 for one instance.  Returns false (kFull =
+  // false only) when the instance has to be routed again by the full variant;
+  // nothing that a second run does not overwrite has been written then.
+  QMG_HD bool run() {
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       S.curQ()[i] = -1;
@@ -2350,6 +2505,9 @@ template <int H> struct Search {
       restoreSharedCircuit();
     }
     g.sync();
+    if (!kFull && rc == ST_NEEDS_FULL) {
+      return false;
+    }
     QMG_NOUNROLL
     for (int i = g.lane; i < n; i += Group::W) {
       I.finalQ[i] = S.curQ()[i];
@@ -2384,6 +2542,7 @@ template <int H> struct Search {
       I.counters[1] = totGenerated;
     }
     g.sync();
+    return true;
   }
 };
 

@@ -1,0 +1,62 @@
+"""Synthetic workloads of BASELINE.json's configs 3 and 4, shared by bench.py
+and the parity tests so that both route exactly the same instances.
+
+config 3: the examples/*.qasm suite on a 27-qubit heavy-hex architecture,
+          circuits x seeded relabellings (= different initial layouts)
+config 4: seeded random 127-qubit circuits on a 127-qubit heavy-hex
+          architecture with synthetic calibration data, fidelity-aware
+          heuristic (fidelity_best_location, HeuristicMapper.cpp:1247-1354)
+"""
+from __future__ import annotations
+
+import os
+import tempfile
+
+import numpy as np
+
+from . import architecture as ar
+from . import circuit as qcirc
+
+C4_CALIBRATION_SEED = 127
+C4_CONFIG = dict(heuristic="fidelity_best_location", lookahead_heuristic="none",
+                 initial_layout="identity")
+C3_CONFIG = dict(initial_layout="identity")
+
+
+def c4_files(directory: str | None = None):
+    """(arch file, calibration csv) of the config-4 architecture, written to
+    `directory` (a fresh temporary directory by default)."""
+    n, cm = ar.heavy_hex_127()
+    d = directory or tempfile.mkdtemp(prefix="qmap_c4_")
+    os.makedirs(d, exist_ok=True)
+    arch_path = os.path.join(d, "heavy_hex_127.arch")
+    csv_path = os.path.join(d, "heavy_hex_127.csv")
+    with open(arch_path, "w") as f:
+        f.write(f"{n}\n" + "\n".join(f"{a} {b}" for a, b in sorted(cm)) + "\n")
+    with open(csv_path, "w") as f:
+        f.write(ar.synthetic_calibration_csv(n, cm, C4_CALIBRATION_SEED))
+    return arch_path, csv_path
+
+
+def c4_circuit(seed: int, n_cx: int) -> qcirc.Circuit:
+    """Instance `seed` of config 4: n_cx CX on uniformly random pairs of the
+    127 qubits, 1q gates in between (circuit.random_circuit)."""
+    return qcirc.random_circuit(127, n_cx, 1000 + seed)
+
+
+def c3_instances(circuit_dir: str, copies: int, first_seed: int = 0, n_physical: int = 27):
+    """[(file name, Circuit)]: every circuit of the suite `copies` times, each
+    copy widened to n_physical qubits and relabelled by a seeded injection of
+    its qubits into them - with the identity initial layout every copy starts
+    from a different placement of the same circuit."""
+    out = []
+    files = sorted(f for f in os.listdir(circuit_dir) if f.endswith(".qasm"))
+    for f in files:
+        base = qcirc.load_qasm(os.path.join(circuit_dir, f))
+        for k in range(copies):
+            rng = np.random.default_rng([first_seed + k, len(f), base.n_qubits])
+            wide = qcirc.Circuit(n_physical, ops=list(base.ops), name=base.name,
+                                 n_clbits=base.n_clbits, measurements=list(base.measurements))
+            perm = rng.permutation(n_physical)
+            out.append((f, wide.relabel(perm)))
+    return out

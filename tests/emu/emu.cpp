@@ -11,6 +11,7 @@
 #include "../../mqt-qmap_b200/csrc/host_api.hpp"
 #include "../../mqt-qmap_b200/csrc/flatten.hpp"
 
+#include <cstdlib>
 #include <memory>
 #include <vector>
 
@@ -72,10 +73,30 @@ QMG_API int qemu_arch_set_fidelity(qemu_arch* a, const double* c1,
 }
 QMG_API void qemu_arch_destroy(qemu_arch* a) { delete a; }
 
+namespace {
+// the kernel's per-instance dispatch (route.cuh): lean variant first, the full
+// one when that gives up (or right away: QMG_EMU_START_FULL=1)
+template <int H>
+void runBoth(const ArchView& A, const CfgView& C, InstView& I, SearchMem& M,
+             Scratch& S, bool startFull) {
+  bool full = startFull;
+  if (!full) {
+    Search<H, false> s(A, C, I, M, S);
+    full = !s.run();
+  }
+  if (full) {
+    Search<H, true> s(A, C, I, M, S);
+    s.run();
+  }
+}
+}  // namespace
+
 QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
                              size_t nInstances, const qmg_instance* instances,
                              qmg_route_result* results, uint32_t poolNodes) {
   static_assert(sizeof(LayerOut) == sizeof(qmg_layer_result), "layer result");
+  const char* sfEnv = std::getenv("QMG_EMU_START_FULL");
+  const bool startFull = sfEnv != nullptr && sfEnv[0] == '1';
   if (const char* msg = checkConfig(*cfg, arch->fidelity)) {
     return fail(QMG_BAD_ARG, msg);
   }
@@ -160,6 +181,8 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.pool = reinterpret_cast<uint8_t*>(poolStore.data());
     M.open = open.data();
     M.table = table.data();
+    std::vector<OpenEntry> btop(poolNodes / kBlk + 2);
+    M.btop = btop.data();
     M.nsw = nsw.data();
     M.poolCap = poolNodes;
     M.recBytes = recBytes;
@@ -200,11 +223,11 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     I.summary = summary;
     I.counters = counters;
     switch (C.heuristic) {
-    case 0: { Search<0> s(A, C, I, M, S); s.run(); break; }
-    case 1: { Search<1> s(A, C, I, M, S); s.run(); break; }
-    case 2: { Search<2> s(A, C, I, M, S); s.run(); break; }
-    case 3: { Search<3> s(A, C, I, M, S); s.run(); break; }
-    default: { Search<4> s(A, C, I, M, S); s.run(); break; }
+    case 0: { runBoth<0>(A, C, I, M, S, startFull); break; }
+    case 1: { runBoth<1>(A, C, I, M, S, startFull); break; }
+    case 2: { runBoth<2>(A, C, I, M, S, startFull); break; }
+    case 3: { runBoth<3>(A, C, I, M, S, startFull); break; }
+    default: { runBoth<4>(A, C, I, M, S, startFull); break; }
     }
     stamp = M.stamp;
     r.n_swaps_total = summary[0];

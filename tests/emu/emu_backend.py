@@ -18,7 +18,11 @@ from qmap_b200 import _abi  # noqa: E402
 
 
 def build(asan: bool = False) -> str:
-    out = os.path.join(HERE, "libqmg_emu_asan.so" if asan else "libqmg_emu.so")
+    # QMG_EMU_BLK="4,8": open-list blocks of 4 entries from 8 open nodes on, so
+    # that the small golden cases exercise the blocked open list
+    blk = os.environ.get("QMG_EMU_BLK", "")
+    out = os.path.join(HERE, "libqmg_emu_asan.so" if asan else
+                       (f"libqmg_emu_blk_{blk.replace(',', '_')}.so" if blk else "libqmg_emu.so"))
     src = os.path.join(HERE, "emu.cpp")
     deps = [src] + [os.path.join(ROOT, "mqt-qmap_b200", "csrc", f)
                     for f in ("route_core.hpp", "layers.hpp", "host_api.hpp", "flatten.hpp")]
@@ -28,6 +32,9 @@ def build(asan: bool = False) -> str:
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     flags = ["-std=c++17", "-fPIC", "-shared", "-Wall", "-Wextra", "-g"]
     flags += ["-O1", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
+    if blk:
+        b, bmin = blk.split(",")
+        flags += [f"-DQMG_BLK={int(b)}", f"-DQMG_BLK_MIN={int(bmin)}"]
     subprocess.check_call([cxx, *flags, "-o", out, src])
     return out
 

@@ -131,3 +131,32 @@ def test_random_circuits_with_layer_splits_against_oracle(arch, calib):
         assert (a.expanded_nodes, a.generated_nodes) == (b.expanded_nodes, b.generated_nodes)
         splits += len(b.split_layers)
     assert splits > 50
+
+
+@pytest.mark.parametrize("env", [{"QMG_EMU_BLK": "4,8"}, {"QMG_EMU_BLK": "7,1"},
+                                 {"QMG_EMU_START_FULL": "1"}])
+def test_full_search_variant_matches_reference_outputs(env):
+    """The kernel routes an instance with the lean search variant and again
+    with the full one (per-block tops of the open list, layer splits) once an
+    open list outgrows kBlkMin.  Built with blocks of 4 (7) entries from 8 (1)
+    open nodes on, the golden cases run through the hand-over and the blocked
+    open list; QMG_EMU_START_FULL=1 uses the full variant from the start."""
+    import subprocess
+    import sys
+    code = (
+        "import sys; sys.path[:0] = [%r, %r, %r]\n"
+        "import emu_backend, parity, test_emu_parity as t\n"
+        "runs = t.RUNS[::6] + t.SPLIT_RUNS[::3]\n"
+        "bad = []\n"
+        "for g in runs:\n"
+        "    be = t.emu_for(g.meta['arch'], g.meta['calibration'])\n"
+        "    msg, _ = parity.run_golden(be, be.lib, be.n, g)\n"
+        "    if msg: bad.append((g.label, msg))\n"
+        "assert len(runs) > 40 and not bad, bad[:3]\n"
+        "print('ok', len(runs))\n"
+    ) % (os.path.dirname(__file__), os.path.join(os.path.dirname(__file__), "emu"),
+         os.path.join(parity.ROOT, "mqt-qmap_b200"))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env),
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.startswith("ok")
