@@ -139,6 +139,108 @@ def run_reference(seeds, cores: int):
             busy, wall, sum(r[4] for r in res))
 
 
+class WorkloadC2:
+    """configs[1]: qft_16 on IBM QX5, seeded relabellings, lookahead."""
+    key = "c2"
+    name = WORKLOAD
+    n = 16
+    default_batch = 16384
+
+    def __init__(self, args):
+        self.args = args
+
+    def cpu_sample(self, cores):
+        return self.args.cpu_sample or 6000 * cores
+
+    def ref_step_sample(self, cores):
+        return self.args.cpu_sample or 600 * cores
+
+    def run_reference(self, seeds, cores):
+        return run_reference(seeds, cores)
+
+    def architecture(self, device):
+        from qmap_b200.architecture import Architecture
+        return Architecture(device=device).load_coupling_map(ARCH)
+
+    def config(self):
+        from qmap_b200 import routing
+        return routing.make_config(initial_layout="identity")
+
+    def items(self, L, n, cfg, seeds):
+        from qmap_b200 import routing
+        from qmap_b200 import circuit as qcirc
+        base = qcirc.load_qasm(QASM)
+        c0, t0_ = base.gate_arrays()
+        out = []
+        for s in seeds:
+            c, t = relabel_arrays(c0, t0_, instance_perm(s))
+            lc = routing.LayeredCircuit(L, n, c, t, cfg.layering)
+            out.append(routing.RouteItem(lc, np.arange(n, dtype=np.int16)))
+        return out
+
+    def options(self, opts):
+        opts.searches_per_sm = self.args.searches_per_sm
+
+
+class WorkloadC4:
+    """configs[3]: random 127-qubit circuits on a 127-qubit heavy-hex
+    architecture with (synthetic) calibration data, fidelity_best_location.
+    The reference's search grows exponentially with the distance of the gate's
+    qubits (10^4..10^5 nodes per layer after ~30 CX), so an instance is the
+    first `--c4-cx` CX of a seeded random circuit instead of 10k CX: the
+    reference routes such an instance in seconds, a 10k-CX one not at all."""
+    key = "c4"
+    n = 127
+    default_batch = 3552
+
+    def __init__(self, args):
+        self.args = args
+        self.n_cx = args.c4_cx
+        self.name = (f"random 127-qubit circuits ({self.n_cx} CX + 1q gates each) on heavy-hex 127 "
+                     "with synthetic calibration, heuristic fidelity_best_location, batch of seeded circuits")
+
+    def cpu_sample(self, cores):
+        return self.args.cpu_sample or 8 * cores
+
+    def ref_step_sample(self, cores):
+        return self.args.cpu_sample or 4 * cores
+
+    def run_reference(self, seeds, cores):
+        return run_reference_c4(seeds, cores, self.n_cx)
+
+    def architecture(self, device):
+        from qmap_b200 import workloads
+        from qmap_b200.architecture import Architecture
+        arch_path, csv_path = workloads.c4_files()
+        a = Architecture(device=device).load_coupling_map(arch_path)
+        a.load_properties(csv_path)
+        return a
+
+    def config(self):
+        from qmap_b200 import routing, workloads
+        return routing.make_config(**workloads.C4_CONFIG)
+
+    def items(self, L, n, cfg, seeds):
+        from qmap_b200 import routing, workloads
+        out = []
+        for s in seeds:
+            circ = workloads.c4_circuit(s, self.n_cx)
+            c, t, identity = circ.mapper_view(n)
+            lc = routing.LayeredCircuit(L, n, c, t, cfg.layering)
+            out.append(routing.RouteItem(lc, identity))
+        return out
+
+    def options(self, opts):
+        # long searches: few resident searches with large node pools (the
+        # budget is most of the HBM), full search variant from the start
+        opts.searches_per_sm = self.args.searches_per_sm or 8
+        opts.search_variant = 1
+        os.environ.setdefault("QMAP_B200_POOL_MB", "100000")
+
+
+WORKLOADS = {"c2": WorkloadC2, "c4": WorkloadC4}
+
+
 def host_cores() -> int:
     try:
         return len(os.sched_getaffinity(0))
@@ -238,92 +340,58 @@ def algorithmic_bytes(n: int, expanded: int, generated: int) -> float:
     return expanded * (R + 16) + generated * (R + 32)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=16384, help="instances per GPU per step")
-    ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = auto)")
-    ap.add_argument("--searches-per-sm", type=int, default=0)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
+def reference_arm(args, wl, cores, config):
+    sample = wl.ref_step_sample(cores)
+    vals = []
+    last = None
+    for step in range(args.warmup + args.steps):
+        seeds = list(range(step * sample, (step + 1) * sample))
+        exp, gen, swaps, busy, wall, search_s = wl.run_reference(seeds, cores)
+        if step >= args.warmup:
+            vals.append((exp, busy))
+        last = (exp, gen, swaps, busy, wall, search_s)
+    tot_e = sum(v[0] for v in vals)
+    tot_t = sum(v[1] for v in vals)
+    v = tot_e / tot_t
+    desc = f"{sample} instances per step on {cores} processes (oracle/_ref = reference sources)"
+    return {
+        "metric": METRIC, "value": v, "unit": "nodes/s", "impl": "reference", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": config,
+        "cpu_baseline": {"value": v, "unit": "nodes/s", "cores": cores, "kind": "reference",
+                         "sample": desc,
+                         "search_loop_only_nodes_per_core_s": last[0] / last[5] if last[5] else None},
+        "e2e": {"value": v, "unit": "nodes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "circuits_per_s": sample * args.steps / tot_t,
+    }
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    cores = host_cores()
-    config = {"workload": WORKLOAD, "batch_per_gpu": args.batch,
-              "l2": "flushed between timed steps (512 MiB write)", "parallelism": f"instances x{world}"}
 
-    if args.impl == "reference":
-        if rank != 0:
-            return
-        sample = args.cpu_sample or 600 * cores
-        vals = []
-        last = None
-        for step in range(args.warmup + args.steps):
-            seeds = list(range(step * sample, (step + 1) * sample))
-            exp, gen, swaps, busy, wall, search_s = run_reference(seeds, cores)
-            if step >= args.warmup:
-                vals.append((exp, busy))
-            last = (exp, gen, swaps, busy, wall, search_s)
-        tot_e = sum(v[0] for v in vals)
-        tot_t = sum(v[1] for v in vals)
-        v = tot_e / tot_t
-        desc = f"{sample} instances per step on {cores} processes (oracle/_ref = reference sources)"
-        print(json.dumps({
-            "metric": METRIC, "value": v, "unit": "nodes/s", "impl": "reference", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": config,
-            "cpu_baseline": {"value": v, "unit": "nodes/s", "cores": cores, "kind": "reference",
-                             "sample": desc,
-                             "search_loop_only_nodes_per_core_s": last[0] / last[5] if last[5] else None},
-            "e2e": {"value": v, "unit": "nodes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "circuits_per_s": sum(1 for _ in range(sample)) * args.steps / tot_t,
-        }))
-        return
+def cpu_baseline_for(wl, cores):
+    sample = wl.cpu_sample(cores)
+    exp, gen, swaps, busy, wall, search_s = wl.run_reference(list(range(sample)), cores)
+    return {"value": exp / busy, "unit": "nodes/s", "cores": cores, "kind": "reference",
+            "sample": f"{sample} seeded instances of the workload (seeds 0..{sample - 1}), "
+                      f"{busy:.1f} s on {cores} processes",
+            "circuits_per_s": sample / busy,
+            "search_loop_only_nodes_per_core_s": exp / search_s if search_s else None}
 
-    # ---- B200 arm ---------------------------------------------------------
-    cpu_base = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        # before CUDA is initialised in this process (workers are spawned)
-        sample = args.cpu_sample or 6000 * cores
-        exp, gen, swaps, busy, wall, search_s = run_reference(list(range(sample)), cores)
-        cpu_base = {"value": exp / busy, "unit": "nodes/s", "cores": cores, "kind": "reference",
-                    "sample": f"{sample} seeded instances of the workload (seeds 0..{sample - 1}), {busy:.1f} s on {cores} processes",
-                    "circuits_per_s": sample / busy,
-                    "search_loop_only_nodes_per_core_s": exp / search_s if search_s else None}
 
-    # one process per GPU shares the host cores for staging
-    os.environ.setdefault("QMAP_B200_THREADS", str(max(2, cores // max(1, world))))
+def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu_base):
+    """One workload on this rank's GPU; returns the JSON line (rank 0) or None."""
     import torch
     import torch.distributed as dist
     from qmap_b200 import _abi, routing
-    from qmap_b200 import circuit as qcirc
-    from qmap_b200.architecture import Architecture
 
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = _abi.load()
-    arch = Architecture(device=local_rank).load_coupling_map(ARCH)
+    arch = wl.architecture(local_rank)
     h = arch.handle
     n = arch.n_qubits
-    base = qcirc.load_qasm(QASM)
-    cfg = routing.make_config(initial_layout="identity")
-    B = args.batch
+    cfg = wl.config()
     seeds = shard_seeds(rank, world, B)
-    items = []
-    c0, t0_ = base.gate_arrays()
-    for s in seeds:
-        c, t = relabel_arrays(c0, t0_, instance_perm(s))
-        lc = routing.LayeredCircuit(L, n, c, t, cfg.layering)
-        items.append(routing.RouteItem(lc, np.arange(n, dtype=np.int16)))
+    items = wl.items(L, n, cfg, seeds)
     opts = _abi.QmgRouteOptions()
-    opts.searches_per_sm = args.searches_per_sm
+    wl.options(opts)
     # what routeCircuit consumes: per-layer SWAP lists + layouts (the per-call
     # benchmark records of config.debug are not requested)
     opts.lean_outputs = 1
@@ -346,12 +414,12 @@ def main():
         _abi.check(L, L.qmg_batch_run(batch, C.byref(stats)))
         return stats.kernel_ms
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     sampler = ClockSampler(local_rank)
     sampler.start()
     barrier()
-    kernel_ms = [step() for _ in range(args.steps)]
+    kernel_ms = [step() for _ in range(steps)]
     barrier()
     clocks = sampler.stop()
     _abi.check(L, L.qmg_batch_fetch(batch, C.addressof(bufs.res)))
@@ -366,7 +434,8 @@ def main():
 
     # e2e: the C-ABI call a host makes, host buffers in and out
     e2e_ms = []
-    for i in range(2 + args.steps):
+    n_e2e = 2 + steps
+    for i in range(n_e2e):
         b2 = routing.pack(n, items, lean=True)
         st2 = _abi.QmgRouteStats()
         torch.cuda.synchronize()
@@ -377,6 +446,7 @@ def main():
         if i >= 2:
             e2e_ms.append(1e3 * dt)
     h2d, d2h = int(st2.h2d_bytes), int(st2.d2h_bytes)
+    e2e_launches = int(st2.kernel_launches)
 
     t_total = sum(kernel_ms) / 1e3
     t_e2e = sum(e2e_ms) / 1e3
@@ -387,10 +457,9 @@ def main():
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     t_total, t_e2e = (float(x) for x in red.tolist())
     exp_all, gen_all, swaps_all, inst_all = (float(x) for x in cnt.tolist())
+    del flush
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
     peaks = {}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -401,16 +470,17 @@ def main():
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f)["route_kernel"]["dram_bytes_per_launch"]
+            traffic = json.load(f)["route_kernel" if wl.key == "c2" else "route_kernel_" + wl.key][
+                "dram_bytes_per_launch"]
     except (OSError, KeyError, ValueError):
         pass
     avg_launch_s = (sum(kernel_ms) / len(kernel_ms)) / 1e3
     abytes = algorithmic_bytes(n, exp, gen)
     achieved = abytes / avg_launch_s / 1e9
-    out = {
-        "metric": METRIC, "value": exp_all * args.steps / t_total, "unit": "nodes/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+    return {
+        "metric": METRIC, "value": exp_all * steps / t_total, "unit": "nodes/s",
+        "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": 1e3 * t_total / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
         "clocks": clocks,
         "e2e": {"value": exp_all * len(e2e_ms) / t_e2e, "unit": "nodes/s",
@@ -418,19 +488,93 @@ def main():
                 "ms_per_step": 1e3 * t_e2e / len(e2e_ms),
                 "circuits_per_s": inst_all * len(e2e_ms) / t_e2e,
                 "outputs": "per-layer SWAP counts + SWAP list + layouts (lean results)",
+                "kernel_launches_per_call": e2e_launches,
                 "last_call_ms": {"stage_h2d": float(st2.h2d_ms), "kernel": float(st2.kernel_ms),
                                  "d2h_scatter": float(st2.d2h_ms)}},
-        "gpu_launches": args.steps,
+        "gpu_launches": steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                      "kernel": "route_kernel", "algorithmic_bytes_per_launch": abytes},
         "cpu_baseline": cpu_base,
-        "circuits_per_s": inst_all * args.steps / t_total,
+        "circuits_per_s": inst_all * steps / t_total,
         "expanded_nodes_per_step": exp_all, "generated_nodes_per_step": gen_all,
         "swaps_per_step": swaps_all, "grid": int(stats.grid), "block": int(stats.block),
     }
-    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
+                    help="c2 = configs[1] (qft_16 on QX5), c4 = configs[3] (127-qubit heavy-hex, fidelity-aware)")
+    ap.add_argument("--batch", type=int, default=0, help="instances per GPU per step (0 = the workload's default)")
+    ap.add_argument("--c4-cx", type=int, default=30, help="CX gates per config-4 instance")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = auto)")
+    ap.add_argument("--searches-per-sm", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="c2 at N=1 also measures config 4 (key 'config4'); this skips it")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cores = host_cores()
+    wl = WORKLOADS[args.workload](args)
+    B = args.batch or wl.default_batch
+
+    def config_of(w, b):
+        return {"workload": w.name, "batch_per_gpu": b,
+                "l2": "flushed between timed steps (512 MiB write)", "parallelism": f"instances x{world}"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        print(json.dumps(reference_arm(args, wl, cores, config_of(wl, B))))
+        return
+
+    # ---- B200 arm ---------------------------------------------------------
+    extra = None
+    if wl.key == "c2" and world == 1 and not args.no_extra:
+        extra = WORKLOADS["c4"](args)
+    cpu_base = cpu_extra = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # before CUDA is initialised in this process (workers are spawned)
+        cpu_base = cpu_baseline_for(wl, cores)
+        if extra is not None:
+            try:
+                cpu_extra = cpu_baseline_for(extra, cores)
+            except Exception as e:  # noqa: BLE001
+                cpu_extra = {"error": repr(e)}
+
+    # one process per GPU shares the host cores for staging
+    os.environ.setdefault("QMAP_B200_THREADS", str(max(2, cores // max(1, world))))
+    import torch
+    import torch.distributed as dist
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    out = b200_arm(args, wl, B, args.steps, args.warmup, rank, world, local_rank,
+                   config_of(wl, B), cpu_base)
+    if extra is not None and out is not None:
+        # configs[3] beside the headline: fewer steps (a step takes seconds)
+        try:
+            Bx = extra.default_batch
+            o4 = b200_arm(args, extra, Bx, min(args.steps, 2), 3, rank, world, local_rank,
+                          config_of(extra, Bx), cpu_extra)
+            keep = ("value", "unit", "steps", "warmup", "ms_per_step", "config", "clocks", "e2e",
+                    "gpu_launches", "roofline", "cpu_baseline", "circuits_per_s",
+                    "expanded_nodes_per_step", "generated_nodes_per_step", "grid", "block")
+            out["config4"] = {k: o4[k] for k in keep}
+        except Exception as e:  # noqa: BLE001
+            out["config4"] = {"error": repr(e)}
+    if out is not None:
+        print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 

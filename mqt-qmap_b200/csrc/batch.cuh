@@ -357,11 +357,18 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   const size_t wOpen =
       lw.add(static_cast<size_t>(nWarps) * poolNodes * sizeof(OpenEntry));
   const size_t wTable = lw.add(static_cast<size_t>(nWarps) * tableSize * 8);
+  // memo of the fidelity-aware best-edge term (SearchMem::pairVal); its tags
+  // follow the hash tables and are cleared with them
+  const size_t pairSlots =
+      cfg->heuristic >= 4 ? static_cast<size_t>(kPairGates) * n * n : 0;
+  const size_t wPairTag = lw.add(static_cast<size_t>(nWarps) * pairSlots * 8);
+  const size_t wPairEnd = lw.size;
+  const size_t wPairVal = lw.add(static_cast<size_t>(nWarps) * pairSlots * 8);
   const size_t btopPerWarp = poolNodes / kBlk + 2;
   const size_t wBtop =
       lw.add(static_cast<size_t>(nWarps) * btopPerWarp * sizeof(OpenEntry));
   b->tableOff = wTable;
-  b->tableBytes = static_cast<size_t>(nWarps) * tableSize * 8;
+  b->tableBytes = wPairEnd - wTable;
 
   if (!W.hin.ensure(b->inSize) || !W.hout.ensure(pinnedOut)) {
     return fail(QMG_OOM, "pinned host allocation failed");
@@ -573,6 +580,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       M.open = at<OpenEntry>(Wk, wOpen) + static_cast<size_t>(w) * poolNodes;
       M.table = at<uint64_t>(Wk, wTable) + static_cast<size_t>(w) * tableSize;
       M.btop = at<OpenEntry>(Wk, wBtop) + static_cast<size_t>(w) * btopPerWarp;
+      if (pairSlots != 0) {
+        M.pairTag = at<uint64_t>(Wk, wPairTag) + static_cast<size_t>(w) * pairSlots;
+        M.pairVal = at<double>(Wk, wPairVal) + static_cast<size_t>(w) * pairSlots;
+      }
       M.nsw = at<uint16_t>(Wk, wNsw) + static_cast<size_t>(w) * 32 * maxG;
       M.poolCap = poolNodes;
       M.recBytes = recBytes;

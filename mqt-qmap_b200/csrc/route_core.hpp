@@ -58,6 +58,7 @@ constexpr uint32_t kScanMax = 96;  // open-list length up to which push() scans
 #define QMG_BLK 512
 #define QMG_BLK_MIN 4096
 #endif
+constexpr uint32_t kPairGates = 2;
 constexpr uint32_t kBlk = QMG_BLK;  // (tests build the host variant with 4 / 8)
 constexpr uint32_t kBlkMin = QMG_BLK_MIN;
 
@@ -218,6 +219,12 @@ struct SearchMem {
   // tops of the kBlk-entry blocks of `open` (kept once the open list is long,
   // see Search::blkEnter): poolCap / kBlk + 2 entries
   OpenEntry* btop;
+  // fidelity-aware scoring, full variant: memo of the best-edge term of the
+  // layer's first kPairGates 2q gates, keyed on the locations (l1, l2) of the
+  // gate's qubits: kPairGates * n * n values and tags; tag = pairKey() of the
+  // aStarMap call that filled the slot.  Null = no memo.
+  double* pairVal;
+  uint64_t* pairTag;
   uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
   uint32_t poolCap, recBytes, tableMask, stamp;
   uint32_t maxG;
@@ -1141,6 +1148,10 @@ template <int H, bool kFull> struct Search {
   // exact, so the lane order does not matter), every ordered sum is done
   // redundantly by all lanes in the reference's order.
   // ------------------------------------------------------------------------
+  // identifies the running aStarMap call (and its restarts after a split)
+  QMG_HD uint64_t pairKey() const {
+    return (static_cast<uint64_t>(M.stamp) << 8) | (M.epoch + 1U);
+  }
   QMG_HD void scoreFidelity(int a, int b, const ParentCosts& pc, Child& out) {
     const bool root = (a == b);
     const int q1 = root ? -2 : pQ[a];
@@ -1214,7 +1225,9 @@ template <int H, bool kFull> struct Search {
       const int loc = locAfter(e.q, q1, q2, a, b);
       const double curr = ldg(A.c1 + loc);
       double best = 0.;
-      QMG_NOUNROLL
+#if defined(__CUDA_ARCH__)
+#pragma unroll 4
+#endif
       for (int p = g.lane; p < n; p += Group::W) {
         const double cp = ldg(A.c1 + p);
         if (cp >= curr) {
@@ -1232,20 +1245,47 @@ template <int H, bool kFull> struct Search {
       const int l1 = locAfter(e.q1, q1, q2, a, b);
       const int l2 = locAfter(e.q2, q1, q2, a, b);
       double sc = DBL_MAX;
-      QMG_NOUNROLL
-      for (int k = g.lane; k < A.nE; k += Group::W) {
-        const int q3 = ldg(A.edges + 2 * k);
-        const int q4 = ldg(A.edges + 2 * k + 1);
-        const double c34 = ldg(A.c2 + q3 * n + q4);
-        const double c43 = ldg(A.c2 + q4 * n + q3);
-        const double v1 = e.fwd * c34 + e.rev * c43 + fidDist(l1, q3, fidK) +
-                          fidDist(l2, q4, fidK);
-        sc = fmin(sc, v1);
-        const double v2 = e.fwd * c43 + e.rev * c34 + fidDist(l2, q3, fidK) +
-                          fidDist(l1, q4, fidK);
-        sc = fmin(sc, v2);
+      // the minimum over the coupling edges depends on (l1, l2) only (gate
+      // multiplicities and table index are fixed for the call): long searches
+      // meet the same pair of locations in many nodes, so the full variant
+      // keeps the value per pair - the same double, computed once
+      bool hit = false;
+      size_t slot = 0;
+      const bool memo = kFull && M.pairVal != nullptr && i < kPairGates;
+      if (memo) {
+        slot = (static_cast<size_t>(i) * n + l1) * n + l2;
+        if (M.pairTag[slot] == pairKey()) {
+          sc = M.pairVal[slot];
+          hit = true;
+        }
       }
-      sc = gmin(g, sc);
+      if (!hit) {
+        // (iterations are independent gathers: unrolled so that they overlap)
+#if defined(__CUDA_ARCH__)
+#pragma unroll 3
+#endif
+        for (int k = g.lane; k < A.nE; k += Group::W) {
+          const int q3 = ldg(A.edges + 2 * k);
+          const int q4 = ldg(A.edges + 2 * k + 1);
+          const double c34 = ldg(A.c2 + q3 * n + q4);
+          const double c43 = ldg(A.c2 + q4 * n + q3);
+          const double v1 = e.fwd * c34 + e.rev * c43 + fidDist(l1, q3, fidK) +
+                            fidDist(l2, q4, fidK);
+          sc = fmin(sc, v1);
+          const double v2 = e.fwd * c43 + e.rev * c34 + fidDist(l2, q3, fidK) +
+                            fidDist(l1, q4, fidK);
+          sc = fmin(sc, v2);
+        }
+        sc = gmin(g, sc);
+        if (memo) {
+          g.sync();
+          if (g.lane == 0) {
+            M.pairVal[slot] = sc;
+            M.pairTag[slot] = pairKey();
+          }
+          g.sync();
+        }
+      }
       if (adjU(l1, l2)) {
         const double currEdge = (e.fwd * ldg(A.c2 + l1 * n + l2) +
                                  e.rev * ldg(A.c2 + l2 * n + l1));
@@ -1353,6 +1393,9 @@ template <int H, bool kFull> struct Search {
   // then narrowed key by key (cost band, validity, heuristic band, valid-gate
   // count, lexicographic layout), which selects the same node as the pairwise
   // order whenever that order is a strict weak order.
+  // kWide: four entries per lane are loaded before they are compared, so that
+  // their memory latencies overlap (long lists: the entries come from L2/HBM)
+  template <bool kWide = false>
   QMG_HD static uint32_t topOfS(const OpenCtx& c, const OpenEntry* arr,
                                 uint32_t lo, uint32_t hi) {
     const Group g;
@@ -1365,8 +1408,24 @@ template <int H, bool kFull> struct Search {
     best.idx = kNone;
     best.nValid = 0;
     best.valid = 0;
+    uint32_t i = lo + g.lane;
+    if (kWide) {
+      QMG_NOUNROLL
+      for (; i + 3 * Group::W < hi; i += 4 * Group::W) {
+        OpenEntry e[4];
+        for (int u = 0; u < 4; ++u) {
+          e[u] = arr[i + u * Group::W];
+        }
+        for (int u = 0; u < 4; ++u) {
+          if (bestPos == kNone || hasPriorityOf(c, e[u], best)) {
+            best = e[u];
+            bestPos = i + u * Group::W;
+          }
+        }
+      }
+    }
     QMG_NOUNROLL
-    for (uint32_t i = lo + g.lane; i < hi; i += Group::W) {
+    for (; i < hi; i += Group::W) {
       const OpenEntry e = arr[i];
       if (bestPos == kNone || hasPriorityOf(c, e, best)) {
         best = e;
@@ -1408,7 +1467,7 @@ template <int H, bool kFull> struct Search {
   // change
   QMG_COLD static uint32_t blkTopOf(OpenCtx c, const OpenEntry* arr, uint32_t lo,
                                     uint32_t hi) {
-    return topOfS(c, arr, lo, hi);
+    return topOfS<true>(c, arr, lo, hi);
   }
   QMG_COLD static void blkRescan(OpenCtx c, const OpenEntry* open,
                                  OpenEntry* btop, uint32_t nOpen, uint32_t b) {
@@ -1585,11 +1644,10 @@ template <int H, bool kFull> struct Search {
         }
         diff = diff || (q[i] != v);
       }
-      if (g.any(diff)) {
-        return false;
-      }
     }
-    return true;
+    // (one vote for the whole layout: equal hashes almost always mean equal
+    // layouts, and the loads of all iterations overlap this way)
+    return !g.any(diff);
   }
 
   // switch from scanning the open list to the layout-keyed hash table

@@ -20,7 +20,7 @@ circs = [qcirc.random_circuit(127, M, 1000 + s) for s in range(B)]
 items = [parity.item_for(L, n, c, cfg) for c in circs]
 opts = _abi.QmgRouteOptions(); opts.lean_outputs = 1; opts.searches_per_sm = spsm; opts.pool_nodes = pool; opts.max_searches = maxs
 be = routing.CudaBackend(L, h)
-for rep in range(3):
+for rep in range(int(os.environ.get("REPS", "3"))):
     bufs = routing.pack(n, items, lean=True)
     st = _abi.QmgRouteStats()
     t0 = time.time()

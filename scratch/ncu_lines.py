@@ -7,7 +7,7 @@ tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, stdout=subprocess.DEVNULL)
 cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
 dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cub)], capture_output=True, text=True).stdout.split("\n")
-start = [i for i, l in enumerate(dis) if ".text._ZN3qmg12route_kernelILi0E" in l and ".section" in l][0]
+start = [i for i, l in enumerate(dis) if ".text._ZN3qmg12route_kernelILi%sE" % (sys.argv[4] if len(sys.argv) > 4 else "0") in l and ".section" in l][0]
 cur = None; addr2line = {}
 pat = re.compile(r"/\*([0-9a-f]{4,})\*/")
 for l in dis[start:]:

@@ -183,6 +183,15 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.table = table.data();
     std::vector<OpenEntry> btop(poolNodes / kBlk + 2);
     M.btop = btop.data();
+    std::vector<double> pairVal;
+    std::vector<uint64_t> pairTag;
+    if (C.heuristic >= 4) {
+      const size_t slots = static_cast<size_t>(kPairGates) * A.n * A.n;
+      pairVal.assign(slots, 0.);
+      pairTag.assign(slots, 0);
+      M.pairVal = pairVal.data();
+      M.pairTag = pairTag.data();
+    }
     M.nsw = nsw.data();
     M.poolCap = poolNodes;
     M.recBytes = recBytes;
