@@ -191,7 +191,7 @@ class WorkloadC4:
     reference routes such an instance in seconds, a 10k-CX one not at all."""
     key = "c4"
     n = 127
-    default_batch = 3552
+    default_batch = 8192
 
     def __init__(self, args):
         self.args = args
@@ -397,10 +397,25 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu_ba
     opts.lean_outputs = 1
     bufs = routing.pack(n, items, lean=True)
     batch = C.c_void_p()
-    _abi.check(L, L.qmg_batch_create(h, C.byref(cfg), len(items), C.addressof(bufs.inst),
-                                     C.byref(opts), C.byref(batch)))
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
     stats = _abi.QmgRouteStats()
+
+    def create_resident():
+        # A resident batch is not re-routed by the library when a node pool
+        # runs out (qmg_route_batch is): halve the resident searches, which
+        # doubles the pools, until every instance fits.
+        for _ in range(5):
+            _abi.check(L, L.qmg_batch_create(h, C.byref(cfg), len(items), C.addressof(bufs.inst),
+                                             C.byref(opts), C.byref(batch)))
+            _abi.check(L, L.qmg_batch_run(batch, C.byref(stats)))
+            _abi.check(L, L.qmg_batch_fetch(batch, C.addressof(bufs.res)))
+            if all(int(r.status) != _abi.QMG_POOL_EXHAUSTED for r in bufs.res):
+                return
+            L.qmg_batch_destroy(batch)
+            opts.max_searches = max(4, int(stats.grid) * 4 // 2)
+        raise RuntimeError("node pools too small for the workload")
+
+    create_resident()
 
     def barrier():
         torch.cuda.synchronize()

@@ -283,19 +283,21 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       size_t freeB = 0, totalB = 0;
       CU(cudaMemGetInfo(&freeB, &totalB));
       W.memBudget = std::min<size_t>(freeB / 2, 16ULL << 30);
-      // QMAP_B200_POOL_MB: the first-tier budget of the node pools (tests use
-      // it to make the pools run out)
+      // QMAP_B200_POOL_MB: the first-tier budget of the node pools, up to 80 %
+      // of the free HBM (long searches want most of it; tests use a tiny one
+      // to make the pools run out)
       if (const char* e = std::getenv("QMAP_B200_POOL_MB")) {
         const long mb = std::atol(e);
         if (mb > 0) {
-          W.memBudget = std::min<size_t>(freeB / 2, static_cast<size_t>(mb) << 20);
+          W.memBudget = std::min<size_t>(freeB / 10 * 8, static_cast<size_t>(mb) << 20);
+          W.poolCapNodes = size_t{1} << 24;
         }
       }
     }
     const size_t budget = W.memBudget;
     const size_t perNode = recBytes + sizeof(OpenEntry) + 4 * sizeof(uint64_t);
     size_t pn = budget / (static_cast<size_t>(nWarps) * perNode);
-    pn = std::min<size_t>(pn, 1U << 18);
+    pn = std::min<size_t>(pn, W.poolCapNodes);
     pn = std::max<size_t>(pn, 1024);
     poolNodes = static_cast<uint32_t>(pn);
   }

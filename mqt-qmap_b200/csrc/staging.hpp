@@ -82,6 +82,7 @@ struct Workspace {
   DevArena in, out, work;
   PinnedBuf hin, hout;
   size_t memBudget = 0;  // device bytes the search pools may take
+  size_t poolCapNodes = size_t{1} << 18;  // automatic pool size, at most
 };
 
 // the few cudaDeviceProp fields the launch geometry needs (the query is slow,
