@@ -34,6 +34,7 @@ for p in (ROOT, os.path.join(ROOT, "mqt-qmap_b200")):
 
 QASM = os.path.join(ROOT, "tests", "golden", "circuits", "qft_16.qasm")
 ARCH = os.path.join(ROOT, "tests", "golden", "arch", "ibm_qx5.arch")
+SUITE = os.path.join(ROOT, "tests", "golden", "circuits")
 WORKLOAD = "qft_16 on IBM QX5 (16q), lookahead gate_count_max_distance x15, batch of seeded relabellings"
 METRIC = "astar_expanded_nodes_per_sec"
 
@@ -238,7 +239,85 @@ class WorkloadC4:
         os.environ.setdefault("QMAP_B200_POOL_MB", "100000")
 
 
-WORKLOADS = {"c2": WorkloadC2, "c4": WorkloadC4}
+def _ref_worker_c3(args):
+    seeds, = args
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "mqt-qmap_b200"))
+    from oracle import refapi
+    from qmap_b200 import architecture as ar
+    from qmap_b200 import workloads
+    R = refapi.Ref()
+    n, cm = ar.heavy_hex_27()
+    ra = R.arch_create(n, sorted(cm))
+    cfg = refapi.make_config(debug=True, **workloads.C3_CONFIG)
+    exp = gen = swaps = 0
+    search_s = 0.0
+    t0 = time.perf_counter()
+    for s in seeds:
+        _, circ = workloads.c3_instance(SUITE, s)
+        c, t = circ.gate_arrays()
+        rr = R.map_gates(ra, circ.n_qubits, c, t, cfg)
+        exp += rr.expanded_nodes
+        gen += rr.generated_nodes
+        swaps += rr.swaps
+        search_s += rr.seconds_per_node * rr.expanded_nodes
+    return exp, gen, swaps, time.perf_counter() - t0, search_s
+
+
+class WorkloadC3:
+    """configs[2]: the examples/*.qasm suite (22 circuits, 3..16 qubits) on a
+    27-qubit heavy-hex architecture, circuits x seeded placements, lookahead
+    (the mapper's defaults)."""
+    key = "c3"
+    n = 27
+    default_batch = 16384
+    name = ("examples/*.qasm suite (22 circuits) on heavy-hex 27, default heuristic + lookahead, "
+            "batch of circuits x seeded placements")
+
+    def __init__(self, args):
+        self.args = args
+
+    def cpu_sample(self, cores):
+        return self.args.cpu_sample or 1500 * cores
+
+    def ref_step_sample(self, cores):
+        return self.args.cpu_sample or 300 * cores
+
+    def run_reference(self, seeds, cores):
+        from concurrent.futures import ProcessPoolExecutor
+        import multiprocessing as mp
+        chunks = [c for c in (list(seeds[i::cores]) for i in range(cores)) if c]
+        t0 = time.perf_counter()
+        with ProcessPoolExecutor(max_workers=len(chunks), mp_context=mp.get_context("spawn")) as ex:
+            res = list(ex.map(_ref_worker_c3, [(c,) for c in chunks]))
+        wall = time.perf_counter() - t0
+        return (sum(r[0] for r in res), sum(r[1] for r in res), sum(r[2] for r in res),
+                max(r[3] for r in res), wall, sum(r[4] for r in res))
+
+    def architecture(self, device):
+        from qmap_b200 import architecture as ar
+        n, cm = ar.heavy_hex_27()
+        return ar.Architecture(n, cm, device=device)
+
+    def config(self):
+        from qmap_b200 import routing, workloads
+        return routing.make_config(**workloads.C3_CONFIG)
+
+    def items(self, L, n, cfg, seeds):
+        from qmap_b200 import routing, workloads
+        out = []
+        for s in seeds:
+            _, circ = workloads.c3_instance(SUITE, s)
+            c, t, identity = circ.mapper_view(n)
+            lc = routing.LayeredCircuit(L, n, c, t, cfg.layering)
+            out.append(routing.RouteItem(lc, identity))
+        return out
+
+    def options(self, opts):
+        opts.searches_per_sm = self.args.searches_per_sm
+
+
+WORKLOADS = {"c2": WorkloadC2, "c3": WorkloadC3, "c4": WorkloadC4}
 
 
 def host_cores() -> int:
@@ -525,7 +604,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS),
-                    help="c2 = configs[1] (qft_16 on QX5), c4 = configs[3] (127-qubit heavy-hex, fidelity-aware)")
+                    help="c2 = configs[1] (qft_16 on QX5), c3 = configs[2] (suite on heavy-hex 27), "
+                         "c4 = configs[3] (127-qubit heavy-hex, fidelity-aware)")
     ap.add_argument("--batch", type=int, default=0, help="instances per GPU per step (0 = the workload's default)")
     ap.add_argument("--c4-cx", type=int, default=30, help="CX gates per config-4 instance")
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU sample (0 = auto)")

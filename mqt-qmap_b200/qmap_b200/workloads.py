@@ -44,19 +44,32 @@ def c4_circuit(seed: int, n_cx: int) -> qcirc.Circuit:
     return qcirc.random_circuit(127, n_cx, 1000 + seed)
 
 
+_c3_bases = {}
+
+
+def c3_suite(circuit_dir: str):
+    """[(file name, Circuit)] of the suite, sorted by file name (cached)."""
+    if circuit_dir not in _c3_bases:
+        files = sorted(f for f in os.listdir(circuit_dir) if f.endswith(".qasm"))
+        _c3_bases[circuit_dir] = [(f, qcirc.load_qasm(os.path.join(circuit_dir, f))) for f in files]
+    return _c3_bases[circuit_dir]
+
+
+def c3_instance(circuit_dir: str, seed: int, n_physical: int = 27):
+    """Instance `seed` of config 3: circuit seed % |suite|, widened to
+    n_physical qubits and relabelled by a seeded injection of its qubits into
+    them - with the identity initial layout every seed starts the circuit from
+    a different placement."""
+    suite = c3_suite(circuit_dir)
+    f, base = suite[seed % len(suite)]
+    rng = np.random.default_rng([seed, len(f), base.n_qubits])
+    wide = qcirc.Circuit(n_physical, ops=list(base.ops), name=base.name,
+                         n_clbits=base.n_clbits, measurements=list(base.measurements))
+    return f, wide.relabel(rng.permutation(n_physical))
+
+
 def c3_instances(circuit_dir: str, copies: int, first_seed: int = 0, n_physical: int = 27):
-    """[(file name, Circuit)]: every circuit of the suite `copies` times, each
-    copy widened to n_physical qubits and relabelled by a seeded injection of
-    its qubits into them - with the identity initial layout every copy starts
-    from a different placement of the same circuit."""
-    out = []
-    files = sorted(f for f in os.listdir(circuit_dir) if f.endswith(".qasm"))
-    for f in files:
-        base = qcirc.load_qasm(os.path.join(circuit_dir, f))
-        for k in range(copies):
-            rng = np.random.default_rng([first_seed + k, len(f), base.n_qubits])
-            wide = qcirc.Circuit(n_physical, ops=list(base.ops), name=base.name,
-                                 n_clbits=base.n_clbits, measurements=list(base.measurements))
-            perm = rng.permutation(n_physical)
-            out.append((f, wide.relabel(perm)))
-    return out
+    """[(file name, Circuit)] for seeds first_seed .. first_seed + copies * |suite|."""
+    k = len(c3_suite(circuit_dir))
+    return [c3_instance(circuit_dir, s, n_physical)
+            for s in range(first_seed, first_seed + copies * k)]
