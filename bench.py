@@ -648,6 +648,8 @@ def main():
 
     # one process per GPU shares the host cores for staging
     os.environ.setdefault("QMAP_B200_THREADS", str(max(2, cores // max(1, world))))
+    # stdout carries the JSON line only: NCCL's banner / debug output to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import torch
     import torch.distributed as dist
 
