@@ -11,8 +11,6 @@
 #include <unordered_map>
 
 #include "derive.cuh"
-#include <cmath>
-
 #include "staging.hpp"
 
 using qmg_workspace = qmg::Workspace;
@@ -573,39 +571,6 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
                             (1 + 2 * instances[y].bidirectional_passes);
         return wx > wy;
       });
-    }
-    // Fidelity-aware searches grow exponentially with the distance between a
-    // gate's qubits (tight heuristic, near-unique costs) and the longest
-    // instance ends the launch, so instances that look long start first:
-    // estimate = sum over the 2q gates of 2^(SWAPs between the gate's qubits
-    // in the start layout).  Scheduling only - results do not depend on it.
-    static const bool noEstimate = std::getenv("QMAP_B200_NO_ESTIMATE") != nullptr;
-    if (cfg->heuristic >= 4 && !noEstimate && nInst > nWarps &&
-        arch->hDist.size() == static_cast<size_t>(n) * n) {
-      std::vector<double> est(nInst, 0.);
-      parallelFor(nInst, 64, [&](size_t i) {
-        const qmg_instance& in = instances[i];
-        if (in.initial_locations == nullptr) {
-          return;
-        }
-        const qmg_layers& ly = in.layers;
-        const uint32_t g2n = ly.gate2q_offsets[ly.n_layers];
-        double e = 0.;
-        for (uint32_t k = 0; k < g2n; ++k) {
-          const qmg_gate2q& gt = ly.gates2q[k];
-          const int p1 = in.initial_locations[gt.q1];
-          const int p2 = in.initial_locations[gt.q2];
-          if (p1 < 0 || p2 < 0) {
-            continue;
-          }
-          const double swaps =
-              arch->hDist[static_cast<size_t>(p1) * n + p2] / kCostBiSwap;
-          e += std::exp2(std::min(swaps, 40.)) * (gt.forward + gt.reverse);
-        }
-        est[i] = e * (1 + 2 * in.bidirectional_passes);
-      });
-      std::stable_sort(order, order + nInst,
-                       [&](uint32_t x, uint32_t y) { return est[x] > est[y]; });
     }
   }
   {

@@ -1670,35 +1670,6 @@ template <int H, bool kFull> struct Search {
     g.sync();
   }
 
-  // Long searches: push() walks table slot -> node record -> open entry, one
-  // dependent L2/HBM access after the other, child after child.  Lane c first
-  // touches what push() will read for child c, so that the chains of all
-  // children of the chunk overlap (loads whose values are dropped: a hint,
-  // the push itself is unchanged).
-  QMG_HD void prefetchDedupe(int cnt) {
-#if defined(__CUDA_ARCH__)
-    if (g.lane < cnt) {
-      const uint64_t h = S.ch()[g.lane].hash;
-      const uint32_t slot = static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
-      const uint64_t e = M.table[slot];
-      if (static_cast<uint32_t>(e >> 32) == M.stamp) {
-        const uint32_t idx = static_cast<uint32_t>(e);
-        const uint8_t* rec = M.pool + static_cast<size_t>(idx) * M.recBytes;
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(rec));
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 128));
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 256));
-        const uint32_t pos = reinterpret_cast<const NodeHdr*>(rec)->openPos;
-        if (pos < nOpen) {
-          asm volatile("prefetch.global.L1 [%0];" ::"l"(M.open + pos));
-        }
-      }
-    }
-    g.sync();
-#else
-    (void)cnt;
-#endif
-  }
-
   // UniquePriorityQueue::push :59-82.  Group-uniform.  Returns false when the
   // node pool is exhausted.  Only nodes in the open list take part in the
   // layout identity (pop erases the membership, :84-93), so short open lists
@@ -2180,9 +2151,6 @@ template <int H, bool kFull> struct Search {
             S.ch()[0].b = 0;
           }
           g.sync();
-        }
-        if (kFull && tableMode) {
-          prefetchDedupe(cnt);
         }
         QMG_NOUNROLL
         for (int c = 0; c < cnt; ++c) {
