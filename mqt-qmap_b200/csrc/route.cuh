@@ -25,8 +25,14 @@ constexpr int kWarpsPerCta = 4;
 // 227 KB of shared memory a CTA can opt into)
 constexpr uint32_t kMaxScratchBytes = 56000;
 
+// (the fidelity-aware instantiation runs at most 12 searches per SM on long
+// searches - the node pools take the HBM - so it may use more registers)
+#ifndef QMG_MIN_CTAS_FID
+#define QMG_MIN_CTAS_FID 3
+#endif
 template <int H>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, QMG_MIN_CTAS)
+__global__ void __launch_bounds__(kWarpsPerCta * 32,
+                                  H == 4 ? QMG_MIN_CTAS_FID : QMG_MIN_CTAS)
     route_kernel(ArchView A, CfgView C, const InstView* __restrict__ inst,
                  const uint32_t* __restrict__ order, uint32_t nInst,
                  SearchMem* __restrict__ mem, uint32_t* __restrict__ ticket,
