@@ -234,7 +234,8 @@ class WorkloadC4:
     def options(self, opts):
         # long searches: few resident searches with large node pools (the
         # budget is most of the HBM), full search variant from the start
-        # (measured: 8 / 12 searches per SM -> 23.3 / 26.2 M nodes/s)
+        # (measured: 8 / 12 searches per SM -> 23.3 / 26.2 M nodes/s; 12 is what
+        # the 168-register fidelity kernel keeps resident)
         opts.searches_per_sm = self.args.searches_per_sm or 12
         opts.search_variant = 1
         os.environ.setdefault("QMAP_B200_POOL_MB", "140000")

@@ -257,7 +257,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
                             : static_cast<uint32_t>(QMG_MIN_CTAS) * kWarpsPerCta;
   // more than the register file admits would only queue idle CTAs
   warpsPerSm = std::min<uint32_t>(
-      warpsPerSm, static_cast<uint32_t>(QMG_MIN_CTAS) * kWarpsPerCta);
+      warpsPerSm,
+      static_cast<uint32_t>(cfg->heuristic >= 4 ? QMG_MIN_CTAS_FID : QMG_MIN_CTAS) *
+          kWarpsPerCta);
   warpsPerSm = std::max<uint32_t>(kWarpsPerCta,
                                   warpsPerSm / kWarpsPerCta * kWarpsPerCta);
   while (warpsPerSm > kWarpsPerCta &&
