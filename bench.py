@@ -617,6 +617,17 @@ def main():
                     help="c2 at N=1 also measures config 4 (key 'config4'); this skips it")
     args = ap.parse_args()
 
+    # stdout carries the JSON line and nothing else: everything libraries
+    # print there while the bench runs (NCCL's version banner, ...) is sent to
+    # stderr, the line itself goes to the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -631,7 +642,7 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        print(json.dumps(reference_arm(args, wl, cores, config_of(wl, B))))
+        emit(reference_arm(args, wl, cores, config_of(wl, B)))
         return
 
     # ---- B200 arm ---------------------------------------------------------
@@ -673,7 +684,7 @@ def main():
         except Exception as e:  # noqa: BLE001
             out["config4"] = {"error": repr(e)}
     if out is not None:
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
