@@ -122,13 +122,15 @@ void qmg_config_default(qmg_config* cfg);
  * std::set<std::pair<uint16_t,uint16_t>>, include/sc/utils.hpp:27-29).
  */
 
-/* Dijkstra::buildTable (src/sc/utils.cpp:26-54): all-pairs cheapest path over
+/* Dijkstra::buildTable (src/sc/utils.cpp:26-54): all-pairs path costs over
  * the undirected view of the coupling map with directed weights
  * edgeWeights[from*n+to]; diagonal 0, unreachable -1.
- * exact_association != 0 reproduces the reference's left-to-right
- * floating-point path sums bit for bit (label-correcting kernel); 0 uses the
- * blocked min-plus Floyd-Warshall kernel (bit-exact for integer weights,
- * <= 1e-9 relative otherwise). */
+ * exact_association != 0 replays the reference's Dijkstra::dijkstra
+ * (:56-89) heap operation by heap operation and returns ITS table bit for
+ * bit; for non-uniform weights that table is not always the table of
+ * shortest paths (the reference rewrites records that sit in its heap).
+ * 0 uses the blocked min-plus Floyd-Warshall kernel: true shortest paths,
+ * equal to the reference's table for uniform weights. */
 int qmg_build_table(uint16_t n, const uint16_t* edges, size_t nEdges,
                     const double* edgeWeights, int exact_association,
                     double* distanceTable, int device);
@@ -140,8 +142,10 @@ int qmg_build_single_edge_skip_table(uint16_t n, const double* distanceTable,
                                      double* edgeSkipDistanceTable, int device);
 
 /* Dijkstra::buildEdgeSkipTable (src/sc/utils.cpp:91-145).  tables receives up
- * to maxTables matrices of n*n doubles; *nTables is the number produced (the
- * reference stops at the first all-zero table and drops it). */
+ * to maxTables matrices of n*n doubles; *nTables is the number the build
+ * produced (the reference stops at the first all-zero table and drops it);
+ * if that is more than maxTables the first maxTables are stored and the call
+ * returns QMG_BUFFER_TOO_SMALL. */
 int qmg_build_edge_skip_table(uint16_t n, const uint16_t* edges, size_t nEdges,
                               const double* edgeWeights, int exact_association,
                               double* tables, size_t maxTables,

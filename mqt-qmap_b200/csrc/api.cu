@@ -3,7 +3,7 @@
 // compute entry point returns QMG_NO_DEVICE.
 #define QMG_HOST_API_IMPL
 #include "host_api.hpp"
-#include "route.cuh"
+#include "route_launch.hpp"
 #include "staging.hpp"
 #include "tables.cuh"
 
@@ -139,40 +139,45 @@ struct EventTimer {
 // --------------------------------------------------------------------------
 struct TopoDev {
   DevBuf<uint16_t> edges;
-  DevBuf<uint32_t> incOff, inc, nbrOff;
-  DevBuf<uint16_t> nbr;
+  DevBuf<uint32_t> incOff, inc;
   DevBuf<uint8_t> adj;
   void upload(const ArchTopology& t) {
     edges.upload(t.edges);
     incOff.upload(t.incOff);
     inc.upload(t.inc);
     adj.upload(t.adj);
-    // undirected neighbour lists for the label-correcting kernel
-    std::vector<uint32_t> off{0};
-    std::vector<uint16_t> nb;
-    for (int v = 0; v < t.n; ++v) {
-      for (int u = 0; u < t.n; ++u) {
-        if (u != v && t.adj[static_cast<size_t>(u) * t.n + v] != 0) {
-          nb.push_back(static_cast<uint16_t>(u));
-        }
-      }
-      off.push_back(static_cast<uint32_t>(nb.size()));
-    }
-    nbrOff.upload(off);
-    nbr.upload(nb);
   }
 };
 
 // Dijkstra::buildTable on the device; w and out are n*n device matrices
-void devBuildTable(int n, const TopoDev& td, const double* w, bool exact,
-                   double* out, cudaStream_t s) {
+// exact: replay the reference's Dijkstra (required for non-uniform weights,
+// where its table is not the table of shortest paths, see tables.cuh K1');
+// otherwise blocked Floyd-Warshall (equal to the reference for uniform weights)
+void devBuildTable(int n, int nE, const TopoDev& td, const double* w,
+                   bool exact, double* out, cudaStream_t s) {
   if (n == 0) {
     return;
   }
   if (exact) {
-    const size_t sm = 2 * static_cast<size_t>(n) * sizeof(double);
-    sssp_exact_kernel<<<n, 256, sm, s>>>(n, w, td.nbrOff.p, td.nbr.p, out);
+    // the reference's own Dijkstra, heap operation by heap operation
+    const int heapCap = 2 * nE + 2;
+    DevBuf<uint8_t> visited;
+    DevBuf<uint16_t> heap;
+    DevBuf<int> overflow;
+    visited.alloc(static_cast<size_t>(n) * n);
+    heap.alloc(static_cast<size_t>(n) * heapCap);
+    overflow.alloc(1);
+    CU(cudaMemsetAsync(overflow.p, 0, sizeof(int), s));
+    dijkstra_reference_kernel<<<(n + 31) / 32, 32, 0, s>>>(
+        n, w, td.edges.p, td.incOff.p, td.inc.p, out, visited.p, heap.p,
+        heapCap, overflow.p);
     CU(cudaGetLastError());
+    int ov = 0;
+    CU(cudaMemcpyAsync(&ov, overflow.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));  // (scratch is freed on return)
+    if (ov != 0) {
+      throw CudaFail{QMG_CUDA_ERROR, "Dijkstra heap capacity exceeded"};
+    }
     return;
   }
   const int nb = (n + kFwTile - 1) / kFwTile;
@@ -210,25 +215,25 @@ void devSingleEdgeSkip(int n, const TopoDev& td, int nE, const double* D,
   CU(cudaGetLastError());
 }
 
-// Dijkstra::buildEdgeSkipTable; returns the tables (device, K*n*n)
+// Dijkstra::buildEdgeSkipTable; returns the number of tables the reference
+// produces.  At most maxTables of them are kept (device, n*n each, in order);
+// level k needs all of T_0..T_{k-1}, so the build itself always holds every
+// level and the surplus is dropped at the end.
 size_t devEdgeSkipTables(int n, const TopoDev& td, int nE, const double* w,
                          bool exact, DevBuf<double>& tables, size_t maxTables,
                          cudaStream_t s) {
   const size_t nn = static_cast<size_t>(n) * n;
+  (void)maxTables;
   // the reference tries k = 1..n and stops at the first all-zero level
-  size_t cap = std::min<size_t>(maxTables, static_cast<size_t>(n) + 1);
-  cap = std::max<size_t>(cap, 1);
+  const size_t cap = static_cast<size_t>(n) + 1;
   size_t alloc = std::min<size_t>(cap, 32);
   tables.alloc(alloc * nn);
-  devBuildTable(n, td, w, exact, tables.p, s);
+  devBuildTable(n, nE, td, w, exact, tables.p, s);
   DevBuf<int> flag;
   flag.alloc(1);
   size_t K = 1;
   for (size_t k = 1; k <= static_cast<size_t>(n); ++k) {
     if (K + 1 > alloc) {
-      if (alloc >= cap) {
-        break;  // caller's capacity reached
-      }
       const size_t na = std::min(cap, alloc * 2);
       DevBuf<double> bigger;
       bigger.alloc(na * nn);
@@ -280,7 +285,7 @@ QMG_API int qmg_build_table(uint16_t n, const uint16_t* edges, size_t nEdges,
     DevBuf<double> w, out;
     w.upload(edgeWeights, nn);
     out.alloc(nn);
-    devBuildTable(n, td, w.p, exact_association != 0, out.p, nullptr);
+    devBuildTable(n, t.nE, td, w.p, exact_association != 0, out.p, nullptr);
     CU(cudaMemcpy(distanceTable, out.p, nn * sizeof(double),
                   cudaMemcpyDeviceToHost));
     return static_cast<int>(QMG_OK);
@@ -330,9 +335,15 @@ QMG_API int qmg_build_edge_skip_table(uint16_t n, const uint16_t* edges,
     w.upload(edgeWeights, nn);
     const size_t K = devEdgeSkipTables(n, td, t.nE, w.p, exact_association != 0,
                                        tb, maxTables, nullptr);
+    // *nTables is the true count; a caller whose buffer was smaller gets the
+    // first maxTables tables and QMG_BUFFER_TOO_SMALL
     *nTables = K;
     CU(cudaMemcpy(tables, tb.p, std::min(K, maxTables) * nn * sizeof(double),
                   cudaMemcpyDeviceToHost));
+    if (K > maxTables) {
+      return fail(QMG_BUFFER_TOO_SMALL, "edge-skip tables: buffer holds fewer "
+                                        "tables than the build produced");
+    }
     return static_cast<int>(QMG_OK);
   });
 }
@@ -420,7 +431,10 @@ QMG_API int qmg_arch_create(uint16_t n, const uint16_t* edges, size_t nEdges,
     a->distRev.alloc(nn);
     EventTimer tm(a->stream);
     tm.start();
-    devBuildTable(n, a->td, dw.p, false, simple.p, a->stream);
+    // uniform SWAP costs (all edges bidirectional, or all unidirectional):
+    // Floyd-Warshall; mixed 30/34: the reference's Dijkstra replayed
+    const bool uniform = t.bidirectional || t.unidirectional;
+    devBuildTable(n, t.nE, a->td, dw.p, !uniform, simple.p, a->stream);
     devSingleEdgeSkip(n, a->td, t.nE, simple.p, 0., a->dist.p, a->stream);
     if (t.bidirectional) {
       CU(cudaMemcpyAsync(a->distRev.p, a->dist.p, nn * sizeof(double),

@@ -94,9 +94,10 @@ struct CircKey {
   const void* b;
   const void* c;
   const void* d;
-  uint32_t nl;
+  uint32_t nl, nLogical;
   bool operator==(const CircKey& o) const {
-    return a == o.a && b == o.b && c == o.c && d == o.d && nl == o.nl;
+    return a == o.a && b == o.b && c == o.c && d == o.d && nl == o.nl &&
+           nLogical == o.nLogical;
   }
 };
 struct CircKeyHash {
@@ -105,7 +106,7 @@ struct CircKeyHash {
     h ^= reinterpret_cast<uintptr_t>(k.b) + 0xBF58476D1CE4E5B9ULL + (h << 6) +
          (h >> 2);
     h ^= reinterpret_cast<uintptr_t>(k.c) * 0x94D049BB133111EBULL + (h >> 29);
-    return static_cast<size_t>(h ^ (h >> 32) ^ k.nl);
+    return static_cast<size_t>(h ^ (h >> 32) ^ k.nl ^ (k.nLogical * 0x9E3779B9U));
   }
 };
 
@@ -172,7 +173,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       return fail(QMG_BAD_ARG, "instance without layers");
     }
     const CircKey key{L.gate2q_offsets, L.gates2q, L.gate1q_offsets, L.gates1q,
-                      L.n_layers};
+                      L.n_layers, L.n_logical};
     size_t slot = CircKeyHash()(key) & (tabSize - 1);
     uint32_t hit = 0;
     while ((hit = tab[slot]) != 0 && !(circKey[hit - 1] == key)) {
@@ -501,10 +502,18 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     const auto& c = circs[circOf[i]];
     int16_t* init = at<int16_t>(H, sInit) + i * n;
     if (instances[i].initial_locations != nullptr) {
+      // locations must be injective: two logical qubits on one physical
+      // qubit would give the search layouts that are not permutations
+      uint64_t used[16] = {};  // n <= 1024 (uint16 qubit ids; checked below)
       for (int q = 0; q < n; ++q) {
         const int16_t p = instances[i].initial_locations[q];
         if (p < -1 || p >= n) {
           badInit.store(1);
+        } else if (p >= 0 && n <= 1024) {
+          if ((used[p >> 6] >> (p & 63)) & 1U) {
+            badInit.store(2);
+          }
+          used[p >> 6] |= uint64_t{1} << (p & 63);
         }
         init[q] = p;
       }
@@ -553,7 +562,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.counters = at<uint64_t>(O, b->oCounters) + 2 * i;
   });
   if (badInit.load() != 0) {
-    return fail(QMG_BAD_ARG, "initial location out of range");
+    return fail(QMG_BAD_ARG, badInit.load() == 2
+                                 ? "two logical qubits on one physical qubit in "
+                                   "initial_locations"
+                                 : "initial location out of range");
   }
   {
     // largest instances first
@@ -615,12 +627,11 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->h2dBytes = b->inSize;
   {
     const int sb = static_cast<int>(b->smemBytes);
-    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-    CU(cudaFuncSetAttribute(route_kernel<0>, attr, sb));
-    CU(cudaFuncSetAttribute(route_kernel<1>, attr, sb));
-    CU(cudaFuncSetAttribute(route_kernel<2>, attr, sb));
-    CU(cudaFuncSetAttribute(route_kernel<3>, attr, sb));
-    CU(cudaFuncSetAttribute(route_kernel<4>, attr, sb));
+    CU(routeSetSharedMemoryH0(sb));
+    CU(routeSetSharedMemoryH1(sb));
+    CU(routeSetSharedMemoryH2(sb));
+    CU(routeSetSharedMemoryH3(sb));
+    CU(routeSetSharedMemoryH4(sb));
   }
   sc.mark("attrs");
   CU(cudaStreamSynchronize(s));
@@ -644,36 +655,34 @@ int batchRun(qmg_batch* b, qmg_route_stats* stats) {
   EventTimer tm(s);
   tm.start();
   if (b->nInst > 0) {
-    const ArchView av = b->arch->view();
-    const uint32_t nI = static_cast<uint32_t>(b->nInst);
-    const dim3 blk(kWarpsPerCta * 32);
-    const InstView* inst = at<InstView>(W.in.p, b->iInst);
-    const uint32_t* order = at<uint32_t>(W.in.p, b->iOrder);
-    SearchMem* mem = at<SearchMem>(W.in.p, b->iMem);
-    uint32_t* ticket = at<uint32_t>(W.out.p, b->oSwapCounter) + 1;
-#define QMG_LAUNCH(HH)                                                         \
-  route_kernel<HH><<<b->grid, blk, b->smemBytes, s>>>(av, b->cfg, inst, order, \
-                                                      nI, mem, ticket, b->sl,  \
-                                                      b->startFull)
+    RouteArgs ra{};
+    ra.A = b->arch->view();
+    ra.C = b->cfg;
+    ra.inst = at<InstView>(W.in.p, b->iInst);
+    ra.order = at<uint32_t>(W.in.p, b->iOrder);
+    ra.nInst = static_cast<uint32_t>(b->nInst);
+    ra.mem = at<SearchMem>(W.in.p, b->iMem);
+    ra.ticket = at<uint32_t>(W.out.p, b->oSwapCounter) + 1;
+    ra.lay = b->sl;
+    ra.startFull = b->startFull;
+    const size_t sm = b->smemBytes;
     switch (b->cfg.heuristic) {
     case 0:
-      QMG_LAUNCH(0);
+      CU(routeLaunchH0(b->grid, sm, s, ra));
       break;
     case 1:
-      QMG_LAUNCH(1);
+      CU(routeLaunchH1(b->grid, sm, s, ra));
       break;
     case 2:
-      QMG_LAUNCH(2);
+      CU(routeLaunchH2(b->grid, sm, s, ra));
       break;
     case 3:
-      QMG_LAUNCH(3);
+      CU(routeLaunchH3(b->grid, sm, s, ra));
       break;
     default:
-      QMG_LAUNCH(4);
+      CU(routeLaunchH4(b->grid, sm, s, ra));
       break;
     }
-#undef QMG_LAUNCH
-    CU(cudaGetLastError());
     ++b->launches;
   }
   const float ms = tm.stop();

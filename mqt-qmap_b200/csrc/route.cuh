@@ -10,26 +10,10 @@
 #include <cuda_runtime.h>
 
 #include "route_core.hpp"
+#include "route_launch.hpp"
 
 namespace qmg {
 
-constexpr int kWarpsPerCta = 4;
-#ifndef QMG_MIN_CTAS
-// 6 CTAs (24 warps, 80 registers/thread) per SM measured best on config 2:
-// 3/4/5/6/8 -> 102/153/166/172/166 M nodes/s (the grid still holds 8 CTAs per
-// SM; the surplus CTAs start as earlier ones drain)
-#define QMG_MIN_CTAS 6
-#endif
-
-// upper bound of the per-warp working set (4 warps of a CTA must fit the
-// 227 KB of shared memory a CTA can opt into)
-constexpr uint32_t kMaxScratchBytes = 56000;
-
-// (the fidelity-aware instantiation runs at most 12 searches per SM on long
-// searches - the node pools take the HBM - so it may use more registers)
-#ifndef QMG_MIN_CTAS_FID
-#define QMG_MIN_CTAS_FID 3
-#endif
 template <int H>
 __global__ void __launch_bounds__(kWarpsPerCta * 32,
                                   H == 4 ? QMG_MIN_CTAS_FID : QMG_MIN_CTAS)

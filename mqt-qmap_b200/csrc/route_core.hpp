@@ -31,7 +31,7 @@
 #else
 #define QMG_HD_RED QMG_HD
 #endif
-#define QMG_COLD __host__ __device__ __noinline__
+#define QMG_COLD inline __host__ __device__ __noinline__
 #else
 #define QMG_COLD inline
 #define QMG_HD_RED inline

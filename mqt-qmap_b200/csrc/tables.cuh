@@ -3,18 +3,26 @@
 //   K1  fw_phase{1,2,3}     blocked min-plus Floyd-Warshall (Dijkstra::buildTable,
 //                           src/sc/utils.cpp:26-89).  32x32 f64 tiles staged in
 //                           shared memory; min-plus has no MMA form, so no
-//                           tensor cores.  Bit-exact for integer weights.
-//   K1' sssp_exact_kernel   label-correcting all-pairs kernel that reproduces
-//                           the reference's left-to-right path sums
-//                           (cost(u) + w(u,v), utils.cpp:77) bit for bit for
-//                           arbitrary f64 weights: fl(+) is monotone, so the
-//                           Bellman-Ford fixed point equals Dijkstra's labels.
+//                           tensor cores.
+//                           Exact shortest paths; equal to the reference's
+//                           table for UNIFORM weights only (see K1').
+//   K1' dijkstra_reference_kernel
+//                           the reference's Dijkstra::dijkstra as it really
+//                           behaves (dijkstra_core.hpp): its heap of pointers
+//                           to records that are rewritten in place can freeze
+//                           a vertex before its label is final, so for
+//                           non-uniform weights (mixed 30/34 SWAP costs,
+//                           fidelity costs) its table differs from the true
+//                           shortest paths.  One thread per source replays the
+//                           same heap operations; bit-exact for any weights.
 //   K2  edge_skip1_kernel   Dijkstra::buildSingleEdgeSkipTable (utils.cpp:147-183)
 //   K2' edge_skipk_kernel   one level of Dijkstra::buildEdgeSkipTable (:91-145)
 #pragma once
 #include <cuda_runtime.h>
 #include <float.h>
 #include <stdint.h>
+
+#include "dijkstra_core.hpp"
 
 namespace qmg {
 
@@ -159,57 +167,26 @@ __global__ void fw_finish(const double* __restrict__ d, int np, int n,
   out[idx] = (r == c) ? 0. : (v >= DBL_MAX ? -1. : v);
 }
 
-// one CTA per source qubit; labels in shared memory (2 * n doubles)
-__global__ void __launch_bounds__(256)
-    sssp_exact_kernel(int n, const double* __restrict__ w,
-                      const uint32_t* __restrict__ nbrOff,
-                      const uint16_t* __restrict__ nbr,
-                      double* __restrict__ out) {
-  extern __shared__ double lab[];
-  double* cur = lab;
-  double* nxt = lab + n;
-  __shared__ int changed;
-  const int src = blockIdx.x;
-  const double inf = __longlong_as_double(0x7ff0000000000000LL);
-  for (int v = threadIdx.x; v < n; v += blockDim.x) {
-    cur[v] = (v == src) ? 0. : inf;
+// K1': one thread per source qubit runs the reference's Dijkstra literally
+// (dijkstra_core.hpp); out row = the labels, scratch = visited flags and heap
+__global__ void __launch_bounds__(32)
+    dijkstra_reference_kernel(int n, const double* __restrict__ w,
+                              const uint16_t* __restrict__ edges,
+                              const uint32_t* __restrict__ incOff,
+                              const uint32_t* __restrict__ inc,
+                              double* __restrict__ out,
+                              uint8_t* __restrict__ visited,
+                              uint16_t* __restrict__ heap, int heapCap,
+                              int* __restrict__ overflow) {
+  const int src = blockIdx.x * blockDim.x + threadIdx.x;
+  if (src >= n) {
+    return;
   }
-  __syncthreads();
-  for (int it = 0; it < n; ++it) {
-    if (threadIdx.x == 0) {
-      changed = 0;
-    }
-    __syncthreads();
-    bool ch = false;
-    for (int v = threadIdx.x; v < n; v += blockDim.x) {
-      double best = cur[v];
-      for (uint32_t k = nbrOff[v]; k < nbrOff[v + 1]; ++k) {
-        const int u = nbr[k];
-        const double cand = cur[u] + w[static_cast<size_t>(u) * n + v];
-        if (cand < best) {
-          best = cand;
-          ch = true;
-        }
-      }
-      nxt[v] = best;
-    }
-    if (ch) {
-      changed = 1;
-    }
-    __syncthreads();
-    double* t = cur;
-    cur = nxt;
-    nxt = t;
-    const int c = changed;
-    __syncthreads();
-    if (c == 0) {
-      break;
-    }
-  }
-  for (int v = threadIdx.x; v < n; v += blockDim.x) {
-    const double d = cur[v];
-    out[static_cast<size_t>(src) * n + v] =
-        (v == src) ? 0. : (d >= DBL_MAX ? -1. : d);
+  double* cost = out + static_cast<size_t>(src) * n;
+  if (!dijkstraReference(n, src, w, edges, incOff, inc, cost,
+                         visited + static_cast<size_t>(src) * n,
+                         heap + static_cast<size_t>(src) * heapCap, heapCap)) {
+    *overflow = 1;
   }
 }
 

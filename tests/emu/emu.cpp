@@ -10,6 +10,7 @@
 #define QMG_HOST_API_IMPL
 #include "../../mqt-qmap_b200/csrc/host_api.hpp"
 #include "../../mqt-qmap_b200/csrc/flatten.hpp"
+#include "../../mqt-qmap_b200/csrc/dijkstra_core.hpp"
 
 #include <cstdlib>
 #include <memory>
@@ -72,6 +73,29 @@ QMG_API int qemu_arch_set_fidelity(qemu_arch* a, const double* c1,
   return QMG_OK;
 }
 QMG_API void qemu_arch_destroy(qemu_arch* a) { delete a; }
+
+// Dijkstra::buildTable through the device function of the table kernel K1'
+// (dijkstra_core.hpp), one source after the other
+QMG_API int qemu_build_table(uint16_t n, const uint16_t* edges, size_t nEdges,
+                             const double* w, double* out) {
+  try {
+    ArchTopology t;
+    t.build(n, edges, nEdges);
+    const int cap = 2 * t.nE + 2;
+    std::vector<uint8_t> visited(n);
+    std::vector<uint16_t> heap(static_cast<size_t>(cap));
+    for (int src = 0; src < n; ++src) {
+      if (!dijkstraReference(n, src, w, t.edges.data(), t.incOff.data(),
+                             t.inc.data(), out + static_cast<size_t>(src) * n,
+                             visited.data(), heap.data(), cap)) {
+        return fail(QMG_BAD_ARG, "heap capacity exceeded");
+      }
+    }
+    return QMG_OK;
+  } catch (const std::exception& e) {
+    return fail(QMG_BAD_ARG, e.what());
+  }
+}
 
 namespace {
 // the kernel's per-instance dispatch (route.cuh): lean variant first, the full

@@ -25,7 +25,8 @@ def build(asan: bool = False) -> str:
                        (f"libqmg_emu_blk_{blk.replace(',', '_')}.so" if blk else "libqmg_emu.so"))
     src = os.path.join(HERE, "emu.cpp")
     deps = [src] + [os.path.join(ROOT, "mqt-qmap_b200", "csrc", f)
-                    for f in ("route_core.hpp", "layers.hpp", "host_api.hpp", "flatten.hpp")]
+                    for f in ("route_core.hpp", "layers.hpp", "host_api.hpp", "flatten.hpp",
+                              "dijkstra_core.hpp")]
     deps.append(os.path.join(ROOT, "include", "qmap_b200.h"))
     if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
         return out
@@ -54,8 +55,19 @@ def lib():
         L.qemu_arch_destroy.restype = None
         L.qemu_route_batch.argtypes = [C.c_void_p, C.POINTER(_abi.QmgConfig), C.c_size_t,
                                        C.c_void_p, C.c_void_p, C.c_uint32]
+        L.qemu_build_table.argtypes = [C.c_uint16, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
+
+
+def build_table(n, edges, weights):
+    """Dijkstra::buildTable by the device function of table kernel K1' (host build)."""
+    L = lib()
+    e = np.ascontiguousarray(edges, dtype=np.uint16).reshape(-1, 2)
+    w = np.ascontiguousarray(weights, dtype=np.float64)
+    out = np.empty((n, n), dtype=np.float64)
+    _abi.check(L, L.qemu_build_table(n, e.ctypes.data, len(e), w.ctypes.data, out.ctypes.data))
+    return out
 
 
 class EmuBackend:

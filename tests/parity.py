@@ -30,6 +30,30 @@ KEYS = ("cost_fixed", "cost_fixed_reversals", "cost_heur", "lookahead_penalty",
 _ref = None
 
 
+DBL_MAX = np.finfo(np.float64).max
+
+
+def random_weighted(n, extra, seed, integer):
+    """Connected random coupling map on n qubits (a spanning tree + `extra`
+    edges, each with probability 1/2 in both directions) and random directed
+    weights; returns (sorted coupling entries, n x n weights, DBL_MAX off-edge)."""
+    rng = np.random.default_rng(seed)
+    und = {(i, int(rng.integers(0, i))) for i in range(1, n)}
+    while len(und) < n - 1 + extra:
+        a, b = (int(x) for x in rng.integers(0, n, 2))
+        if a != b and (b, a) not in und:
+            und.add((a, b))
+    w = np.full((n, n), DBL_MAX)
+    cm = []
+    for a, b in und:
+        cm.append((a, b))
+        if rng.random() < 0.5:
+            cm.append((b, a))
+        for x, y in ((a, b), (b, a)):
+            w[x, y] = float(rng.integers(1, 40)) if integer else float(rng.uniform(0.01, 3.0))
+    return sorted(set(cm)), w
+
+
 def ref() -> refapi.Ref:
     global _ref
     if _ref is None:

@@ -1,5 +1,5 @@
-"""-m gpu: the table kernels (K1 blocked Floyd-Warshall, K1' exact label
-correcting, K2 single-edge-skip, K2' k-edge-skip) against the compiled
+"""-m gpu: the table kernels (K1 blocked Floyd-Warshall, K1' replay of the
+reference's Dijkstra, K2 single-edge-skip, K2' k-edge-skip) against the compiled
 reference (oracle/_ref), through the C ABI."""
 import ctypes as C
 import glob
@@ -51,39 +51,49 @@ def gpu_edge_skip(n, cm, w, exact):
     return out[: k.value].copy()
 
 
-def random_weighted(n, extra, seed, integer):
-    rng = np.random.default_rng(seed)
-    und = {(i, int(rng.integers(0, i))) for i in range(1, n)}
-    while len(und) < n - 1 + extra:
-        a, b = (int(x) for x in rng.integers(0, n, 2))
-        if a != b and (b, a) not in und:
-            und.add((a, b))
-    w = np.full((n, n), DBL_MAX)
-    cm = []
-    for a, b in und:
-        cm.append((a, b))
-        if rng.random() < 0.5:
-            cm.append((b, a))
-        for x, y in ((a, b), (b, a)):
-            w[x, y] = float(rng.integers(1, 40)) if integer else float(rng.uniform(0.01, 3.0))
-    return sorted(set(cm)), w
+random_weighted = parity.random_weighted
+
+
+def _true_shortest(n, cm, w):
+    d = np.full((n, n), np.inf)
+    for a, b in cm:
+        d[a, b] = min(d[a, b], w[a, b])
+        d[b, a] = min(d[b, a], w[b, a])
+    np.fill_diagonal(d, 0.0)
+    for k in range(n):
+        d = np.minimum(d, d[:, k:k + 1] + d[k:k + 1, :])
+    return d
 
 
 @pytest.mark.parametrize("n,extra,seed", [(4, 1, 0), (10, 5, 1), (33, 20, 2), (70, 60, 3), (129, 100, 4)])
-def test_build_table_integer_weights_both_kernels(n, extra, seed):
+def test_build_table_integer_weights(n, extra, seed):
+    """K1' replays the reference's Dijkstra (bit for bit, any weights); K1
+    (Floyd-Warshall) gives the true shortest paths, which is what the reference
+    returns for uniform weights only."""
     cm, w = random_weighted(n, extra, seed, integer=True)
-    want = parity.ref().build_table(n, cm, w)
-    assert np.array_equal(gpu_build_table(n, cm, w, exact=False), want)
-    assert np.array_equal(gpu_build_table(n, cm, w, exact=True), want)
+    assert np.array_equal(gpu_build_table(n, cm, w, exact=True), parity.ref().build_table(n, cm, w))
+    assert np.array_equal(gpu_build_table(n, cm, w, exact=False), _true_shortest(n, cm, w))
+    wu = np.where(w < DBL_MAX, 30.0, DBL_MAX)
+    assert np.array_equal(gpu_build_table(n, cm, wu, exact=False), parity.ref().build_table(n, cm, wu))
+
+
+@pytest.mark.parametrize("integer", [True, False])
+def test_build_table_replay_240_seeds(integer):
+    """Seeds 100..339 include the ones on which the reference's table is not
+    the table of shortest paths (129, 134, 167, 175, 182, ...)."""
+    R = parity.ref()
+    for seed in range(100, 340):
+        n = 12 if seed % 3 else 30
+        cm, w = random_weighted(n, 10 if n == 12 else 25, seed, integer)
+        assert np.array_equal(gpu_build_table(n, cm, w, exact=True), R.build_table(n, cm, w)), seed
 
 
 @pytest.mark.parametrize("n,extra,seed", [(7, 3, 5), (40, 30, 6), (127, 40, 7)])
 def test_build_table_float_weights(n, extra, seed):
     cm, w = random_weighted(n, extra, seed, integer=False)
-    want = parity.ref().build_table(n, cm, w)
-    # exact association: bit for bit; Floyd-Warshall: <= 1e-9 relative
-    assert np.array_equal(gpu_build_table(n, cm, w, exact=True), want)
-    np.testing.assert_allclose(gpu_build_table(n, cm, w, exact=False), want, rtol=1e-9)
+    assert np.array_equal(gpu_build_table(n, cm, w, exact=True), parity.ref().build_table(n, cm, w))
+    np.testing.assert_allclose(gpu_build_table(n, cm, w, exact=False), _true_shortest(n, cm, w),
+                               rtol=1e-9)
 
 
 @pytest.mark.parametrize("rev", [0.0, 1.0, 4.0])
@@ -94,7 +104,9 @@ def test_single_edge_skip(rev):
     assert np.array_equal(gpu_single_skip(50, cm, d, rev), want)
 
 
-@pytest.mark.parametrize("n,extra,seed,integer", [(10, 4, 9, True), (24, 10, 10, False)])
+@pytest.mark.parametrize("n,extra,seed,integer",
+                         [(10, 4, 9, True), (24, 10, 10, False)] +
+                         [(12, 8, s, bool(s & 1)) for s in range(120, 220, 5)])
 def test_edge_skip_tables(n, extra, seed, integer):
     cm, w = random_weighted(n, extra, seed, integer)
     want = parity.ref().build_edge_skip_table(n, cm, w)
@@ -107,8 +119,18 @@ def _arch_cases():
     cases = [(os.path.basename(f), None) for f in sorted(glob.glob(os.path.join(parity.ARCHS, "*.arch")))]
     cases += [("heavy_hex_27", ar.heavy_hex_27), ("heavy_hex_127", ar.heavy_hex_127),
               ("grid_8x8", lambda: ar.grid(8, 8)), ("line_129", lambda: ar.line(129)),
+              ("grid_16x16", lambda: ar.grid(16, 16)),
               ("line_12_directed", lambda: ar.line(12, False))]
+    # mixed directions (30 / 34 SWAP costs): the reference's Dijkstra is replayed
+    for seed in range(12):
+        cases.append((f"mixed_{seed}", lambda seed=seed: _mixed(seed)))
     return cases
+
+
+def _mixed(seed):
+    n = 10 + 3 * seed
+    cm, _ = random_weighted(n, n // 2 + seed, 500 + seed, True)
+    return n, cm
 
 
 @pytest.mark.parametrize("name,gen", _arch_cases())
@@ -149,4 +171,30 @@ def test_fidelity_tables_heavy_hex_127(tmp_path):
     got = a.fidelity_distance_tables()
     assert got.shape == want.shape
     np.testing.assert_allclose(got, want, rtol=1e-9, atol=0)
+    assert np.array_equal(got, want)
+
+
+def test_architecture_distance_tables_grid_32x32():
+    """config 5's architecture (n = 1024); the reference needs about a minute."""
+    n, cm = ar.grid(32, 32)
+    a = ar.Architecture(n, cm)
+    ra = parity.ref().arch_create(n, sorted(cm))
+    assert np.array_equal(a.distance_table(False), ra.distance_table(False))
+    assert np.array_equal(a.distance_table(True), ra.distance_table(True))
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_fidelity_tables_random_calibration_grid_4x4(tmp_path, seed):
+    """heterogeneous calibration: SWAP costs differ per edge, so the k-edge-skip
+    tables start from the replayed Dijkstra (1 of 40 such tables
+    differed with a true shortest-path kernel)."""
+    n, cm = ar.grid(4, 4)
+    a = ar.Architecture(n, cm)
+    (tmp_path / "g.arch").write_text(a.to_arch_text())
+    (tmp_path / "g.csv").write_text(ar.synthetic_calibration_csv(n, cm, 9000 + seed))
+    a.load_properties(str(tmp_path / "g.csv"))
+    ra = parity.ref().arch_load(str(tmp_path / "g.arch"), str(tmp_path / "g.csv"))
+    want = ra.fidelity_distance_tables()
+    got = a.fidelity_distance_tables()
+    assert got.shape == want.shape
     assert np.array_equal(got, want)
