@@ -278,8 +278,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
         1, std::min(b->grid, opt->max_searches / kWarpsPerCta));
   }
   const uint32_t nWarps = b->grid * kWarpsPerCta;
-  const uint32_t recBytes =
-      static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
+  const uint32_t recBytes = nodeRecBytes(n);
   uint32_t poolNodes = (opt != nullptr) ? opt->pool_nodes : 0U;
   if (poolNodes == 0) {
     if (W.memBudget == 0) {
@@ -302,7 +301,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     size_t pn = budget / (static_cast<size_t>(nWarps) * perNode);
     pn = std::min<size_t>(pn, W.poolCapNodes);
     pn = std::max<size_t>(pn, 1024);
-    poolNodes = static_cast<uint32_t>(pn);
+    poolNodes = static_cast<uint32_t>(std::min<size_t>(pn, kMaxPoolNodes));
+  }
+  if (poolNodes > kMaxPoolNodes) {
+    return fail(QMG_BAD_ARG, "pool_nodes exceeds 2^26 - 1 nodes per search");
   }
   b->poolNodes = poolNodes;
   {
@@ -366,9 +368,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   // follow the hash tables and are cleared with them
   const size_t pairSlots =
       cfg->heuristic >= 4 ? static_cast<size_t>(kPairGates) * n * n : 0;
-  const size_t wPairTag = lw.add(static_cast<size_t>(nWarps) * pairSlots * 8);
+  const size_t wPair =
+      lw.add(static_cast<size_t>(nWarps) * pairSlots * sizeof(PairSlot));
   const size_t wPairEnd = lw.size;
-  const size_t wPairVal = lw.add(static_cast<size_t>(nWarps) * pairSlots * 8);
   const size_t btopPerWarp = poolNodes / kBlk + 2;
   const size_t wBtop =
       lw.add(static_cast<size_t>(nWarps) * btopPerWarp * sizeof(OpenEntry));
@@ -597,8 +599,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       M.table = at<uint64_t>(Wk, wTable) + static_cast<size_t>(w) * tableSize;
       M.btop = at<OpenEntry>(Wk, wBtop) + static_cast<size_t>(w) * btopPerWarp;
       if (pairSlots != 0) {
-        M.pairTag = at<uint64_t>(Wk, wPairTag) + static_cast<size_t>(w) * pairSlots;
-        M.pairVal = at<double>(Wk, wPairVal) + static_cast<size_t>(w) * pairSlots;
+        M.pair = at<PairSlot>(Wk, wPair) + static_cast<size_t>(w) * pairSlots;
       }
       M.nsw = at<uint16_t>(Wk, wNsw) + static_cast<size_t>(w) * 32 * maxG;
       M.poolCap = poolNodes;
@@ -855,8 +856,8 @@ QMG_API int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
     // ---- instances whose node pool ran out: again, with fewer resident
     // searches and pools 16 times as large, out of most of the free HBM
     uint64_t pool = b->poolNodes;
-    const size_t perNode = ((sizeof(NodeHdr) + 4U * static_cast<size_t>(b->n) + 7U) & ~size_t{7}) +
-                           sizeof(OpenEntry) + 4 * sizeof(uint64_t) + 1;
+    const size_t perNode = nodeRecBytes(b->n) + sizeof(OpenEntry) +
+                           4 * sizeof(uint64_t) + 1;
     bool retried = false;
     for (int tier = 0; tier < 3; ++tier) {
       std::vector<size_t> idx;
@@ -874,7 +875,7 @@ QMG_API int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
       size_t freeB = 0, totalB = 0;
       CU(cudaMemGetInfo(&freeB, &totalB));
       const size_t budget = freeB / 10 * 8;
-      pool = std::min<uint64_t>(pool * 16, 1ULL << 26);
+      pool = std::min<uint64_t>(pool * 16, kMaxPoolNodes);
       pool = std::min<uint64_t>(pool, budget / (kWarpsPerCta * perNode));
       qmg_route_options o2{};
       if (options != nullptr) {

@@ -19,6 +19,7 @@
 #include <stdint.h>
 #include <float.h>
 #include <math.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define QMG_HD __host__ __device__ __forceinline__
@@ -51,7 +52,12 @@ constexpr int kChunk = 32;    // children scored per pass
 constexpr int kLookBlock = 16; // lookahead layers scored per pass
 // lookahead scratch: a (kChunk/2) x kLookBlock block of terms
 constexpr int kLookPenDoubles = (kChunk / 2) * kLookBlock;
-constexpr uint32_t kScanMax = 96;  // open-list length up to which push() scans
+#ifndef QMG_SCAN_MAX
+#define QMG_SCAN_MAX 96
+#endif
+// open-list length up to which push() scans (tests build the host variant
+// with a small value so that short golden searches use the hash table)
+constexpr uint32_t kScanMax = QMG_SCAN_MAX;
 // open lists longer than kBlkMin keep the top of every kBlk-entry block, so
 // that a pop reads the block tops and re-scans one block instead of the list
 #ifndef QMG_BLK
@@ -175,7 +181,12 @@ struct InstView {
   uint64_t* counters;  // [0]=expanded [1]=generated (all passes)
 };
 
-struct NodeHdr {  // 72 bytes, followed by qubits[n], locations[n]
+// entries of one layout array in a node record: n rounded up to a multiple of
+// 4, so that both arrays start on 8-byte boundaries and are moved as 64-bit
+// words
+QMG_HD uint32_t padN(int n) { return (static_cast<uint32_t>(n) + 3U) & ~3U; }
+
+struct NodeHdr {  // 72 bytes, followed by qubits[padN(n)], locations[padN(n)]
   double fixed, rev, heur, look;
   uint64_t hash;
   uint32_t parent, shared;
@@ -193,6 +204,10 @@ struct NodeHdr {  // 72 bytes, followed by qubits[n], locations[n]
   uint16_t epoch, extra;
 };
 static_assert(sizeof(NodeHdr) == 72, "NodeHdr layout");
+// bytes of one node record
+inline uint32_t nodeRecBytes(int n) {
+  return static_cast<uint32_t>(sizeof(NodeHdr)) + 4U * padN(n);
+}
 
 struct OpenEntry {  // 32 bytes
   double f, h2;
@@ -200,6 +215,33 @@ struct OpenEntry {  // 32 bytes
   uint32_t idx;
   uint16_t nValid;
   uint16_t valid;
+};
+
+// entry of the layout-keyed hash table (SearchMem::table), 64 bits:
+// [stamp:24][hash bits 50..63:14][pool index:26].  stamp identifies the
+// running aStarMap call (0 = never written); the hash bits spare the probe a
+// dependent read of the node record; a match is always confirmed by comparing
+// the layouts.
+constexpr uint32_t kStampMask = 0xFFFFFFU;
+constexpr uint32_t kTabIdxMask = 0x3FFFFFFU;
+constexpr uint32_t kMaxPoolNodes = kTabIdxMask;  // per search
+QMG_HD uint64_t tabPack(uint32_t stamp, uint64_t hash, uint32_t idx) {
+  return (static_cast<uint64_t>(stamp & kStampMask) << 40) |
+         (((hash >> 50) & 0x3FFFULL) << 26) | idx;
+}
+QMG_HD uint32_t tabStamp(uint64_t e) { return static_cast<uint32_t>(e >> 40); }
+QMG_HD uint32_t tabIdx(uint64_t e) {
+  return static_cast<uint32_t>(e) & kTabIdxMask;
+}
+QMG_HD bool tabHashEq(uint64_t e, uint64_t hash) {
+  return ((e >> 26) & 0x3FFFULL) == ((hash >> 50) & 0x3FFFULL);
+}
+
+// one slot of the fidelity best-edge memo: the value and the aStarMap call
+// (pairKey) that computed it, read with one 16-byte load
+struct alignas(16) PairSlot {
+  uint64_t tag;
+  double val;
 };
 
 struct Child {
@@ -221,10 +263,10 @@ struct SearchMem {
   OpenEntry* btop;
   // fidelity-aware scoring, full variant: memo of the best-edge term of the
   // layer's first kPairGates 2q gates, keyed on the locations (l1, l2) of the
-  // gate's qubits: kPairGates * n * n values and tags; tag = pairKey() of the
-  // aStarMap call that filled the slot.  Null = no memo.
-  double* pairVal;
-  uint64_t* pairTag;
+  // gate's qubits: kPairGates * n * n slots; tag = pairKey() of the aStarMap
+  // call that filled the slot.  Null = no memo.
+  PairSlot* pair;
+  uint64_t reserved0;
   uint16_t* nsw;  // scratch for heuristic 2/3: kChunk * maxG
   uint32_t poolCap, recBytes, tableMask, stamp;
   uint32_t maxG;
@@ -330,6 +372,16 @@ struct Group {
   template <class T> QMG_D T xorv(T v, int d) const {
     return __shfl_xor_sync(0xffffffffU, v, d);
   }
+  // lanes (of those with p set) that hold the same value; 0 for a lane
+  // without p.  Called by the whole group.
+  QMG_D uint32_t matchAny(bool p, uint64_t v) const {
+    const uint32_t mask = __ballot_sync(0xffffffffU, p);
+    uint32_t r = 0;
+    if (p) {
+      r = __match_any_sync(mask, v);
+    }
+    return r;
+  }
 };
 #else
 struct Group {
@@ -341,6 +393,7 @@ struct Group {
   template <class T> T bcast(T v, int) const { return v; }
   template <class T> T down(T v, int) const { return v; }
   template <class T> T xorv(T v, int) const { return v; }
+  uint32_t matchAny(bool p, uint64_t) const { return p ? 1U : 0U; }
 };
 #endif
 
@@ -391,6 +444,24 @@ QMG_HD Gate1 ldGate1(const Gate1* p) {
   return g;
 #else
   return *p;
+#endif
+}
+
+// 64-bit words of int16 arrays (8-byte aligned)
+QMG_HD uint64_t ld64(const int16_t* p) {
+#if defined(__CUDA_ARCH__)
+  return *reinterpret_cast<const uint64_t*>(p);
+#else
+  uint64_t v;
+  memcpy(&v, p, 8);
+  return v;
+#endif
+}
+QMG_HD void st64(int16_t* p, uint64_t v) {
+#if defined(__CUDA_ARCH__)
+  *reinterpret_cast<uint64_t*>(p) = v;
+#else
+  memcpy(p, &v, 8);
 #endif
 }
 
@@ -780,7 +851,7 @@ template <int H, bool kFull> struct Search {
     return reinterpret_cast<int16_t*>(
         M.pool + static_cast<size_t>(idx) * M.recBytes + sizeof(NodeHdr));
   }
-  QMG_HD int16_t* nodeL(uint32_t idx) const { return nodeQ(idx) + n; }
+  QMG_HD int16_t* nodeL(uint32_t idx) const { return nodeQ(idx) + padN(n); }
   QMG_HD bool considered(int q) const {
     return (S.consMask()[q >> 5] >> (q & 31)) & 1U;
   }
@@ -1143,165 +1214,211 @@ template <int H, bool kFull> struct Search {
   // ------------------------------------------------------------------------
   // fidelity-aware scoring (recalculateFixedCostFidelity :821-859, the
   // fidelity branches of applySWAP :893-952, heuristicFidelityBestLocation
-  // :1262-1354).  Executed by the WHOLE group for one child; the scans over
-  // physical qubits / coupling edges are spread over the lanes (min / max are
-  // exact, so the lane order does not matter), every ordered sum is done
-  // redundantly by all lanes in the reference's order.
+  // :1262-1354).
   // ------------------------------------------------------------------------
   // identifies the running aStarMap call (and its restarts after a split)
   QMG_HD uint64_t pairKey() const {
     return (static_cast<uint64_t>(M.stamp) << 8) | (M.epoch + 1U);
   }
-  QMG_HD void scoreFidelity(int a, int b, const ParentCosts& pc, Child& out) {
-    const bool root = (a == b);
-    const int q1 = root ? -2 : pQ[a];
-    const int q2 = root ? -2 : pQ[b];
-    if (root) {
-      a = b = -1;
-    }
-    double fixed = root ? 0. : pc.fixed;
-    if (root) {
-      QMG_NOUNROLL
-      for (uint32_t i = 0; i < G1; ++i) {
-        const Gate1 e = ldGate1(gates1 + i);
-        fixed += e.mult * ldg(A.c1 + pL[e.q]);
-      }
-    }
-    uint32_t nValid = (root || !kFull) ? 0U : M.childExtra;
+  // Scores the cnt nodes of S.ch() (root: the layout itself), ONE CHILD PER
+  // LANE: everything that is a chain of dependent table reads (validity of the
+  // gates, fixed-cost deltas, memo look-ups) runs for all children at once;
+  // the scans over physical qubits / coupling edges are done by the whole
+  // group for one child at a time, and only for children that need them (the
+  // best-edge term is usually found in the memo).  Sums are accumulated per
+  // child in the reference's order.
+  QMG_HD void scoreFidelityChunk(int cnt, bool root, const ParentCosts& pc) {
     QMG_NOUNROLL
-    for (uint32_t i = 0; i < G; ++i) {
-      const Gate2 e = ldGate(gates + i);
-      const int p3 = locAfter(e.q1, q1, q2, a, b);
-      const int p4 = locAfter(e.q2, q1, q2, a, b);
-      const bool valid = adjU(p3, p4);
-      nValid += valid ? 1U : 0U;
-      if (root) {
-        if (valid) {
-          fixed += (e.fwd * ldg(A.c2 + p3 * n + p4) +
-                    e.rev * ldg(A.c2 + p4 * n + p3));
+    for (int c0 = 0; c0 < cnt; c0 += Group::W) {
+      const int c = c0 + g.lane;
+      const bool act = c < cnt;
+      int a = -1, b = -1, q1 = -2, q2 = -2;
+      if (act && !root) {
+        a = S.ch()[c].a;
+        b = S.ch()[c].b;
+        q1 = pQ[a];
+        q2 = pQ[b];
+      }
+      double fixed = root ? 0. : pc.fixed;
+      uint32_t nValid = (root || !kFull) ? 0U : M.childExtra;
+      if (act) {
+        if (root) {
+          QMG_NOUNROLL
+          for (uint32_t i = 0; i < G1; ++i) {
+            const Gate1 e = ldGate1(gates1 + i);
+            fixed += e.mult * ldg(A.c1 + pL[e.q]);
+          }
         }
-        continue;
-      }
-      const bool touched =
-          (e.q1 == q1 || e.q1 == q2 || e.q2 == q1 || e.q2 == q2);
-      if (!touched) {
-        continue;
-      }
-      const int o3 = pL[e.q1];
-      const int o4 = pL[e.q2];
-      const bool before = adjU(o3, o4);
-      if (valid && !before) {
-        fixed += e.fwd * ldg(A.c2 + p3 * n + p4) +
-                 e.rev * ldg(A.c2 + p4 * n + p3);
-      } else if (!valid && before) {
-        fixed -= e.fwd * ldg(A.c2 + o3 * n + o4) +
-                 e.rev * ldg(A.c2 + o4 * n + o3);
-      }
-    }
-    if (!root) {
-      // :934-952
-      int m1 = 0;
-      int m2 = 0;
-      QMG_NOUNROLL
-      for (uint32_t i = 0; i < G1; ++i) {
-        const Gate1 e = ldGate1(gates1 + i);
-        if (e.q == q1) {
-          m1 = e.mult;
+        QMG_NOUNROLL
+        for (uint32_t i = 0; i < G; ++i) {
+          const Gate2 e = ldGate(gates + i);
+          const int p3 = locAfter(e.q1, q1, q2, a, b);
+          const int p4 = locAfter(e.q2, q1, q2, a, b);
+          const bool valid = adjU(p3, p4);
+          nValid += valid ? 1U : 0U;
+          if (root) {
+            if (valid) {
+              fixed += (e.fwd * ldg(A.c2 + p3 * n + p4) +
+                        e.rev * ldg(A.c2 + p4 * n + p3));
+            }
+            continue;
+          }
+          const bool touched =
+              (e.q1 == q1 || e.q1 == q2 || e.q2 == q1 || e.q2 == q2);
+          if (!touched) {
+            continue;
+          }
+          const int o3 = pL[e.q1];
+          const int o4 = pL[e.q2];
+          const bool before = adjU(o3, o4);
+          if (valid && !before) {
+            fixed += e.fwd * ldg(A.c2 + p3 * n + p4) +
+                     e.rev * ldg(A.c2 + p4 * n + p3);
+          } else if (!valid && before) {
+            fixed -= e.fwd * ldg(A.c2 + o3 * n + o4) +
+                     e.rev * ldg(A.c2 + o4 * n + o3);
+          }
         }
-        if (e.q == q2) {
-          m2 = e.mult;
+        if (!root) {
+          // :934-952
+          int m1 = 0;
+          int m2 = 0;
+          QMG_NOUNROLL
+          for (uint32_t i = 0; i < G1; ++i) {
+            const Gate1 e = ldGate1(gates1 + i);
+            if (e.q == q1) {
+              m1 = e.mult;
+            }
+            if (e.q == q2) {
+              m2 = e.mult;
+            }
+          }
+          fixed += ((m2 - m1) * ldg(A.c1 + a) + (m1 - m2) * ldg(A.c1 + b));
+          fixed += ldg(A.cswap + a * n + b);
         }
       }
-      fixed += ((m2 - m1) * ldg(A.c1 + a) + (m1 - m2) * ldg(A.c1 + b));
-      fixed += ldg(A.cswap + a * n + b);
-    }
 
-    // heuristicFidelityBestLocation
-    double costHeur = 0.;
-    double savings = 0.;
-    QMG_NOUNROLL
-    for (uint32_t i = 0; i < G1; ++i) {
-      const Gate1 e = ldGate1(gates1 + i);
-      const int loc = locAfter(e.q, q1, q2, a, b);
-      const double curr = ldg(A.c1 + loc);
-      double best = 0.;
+      // heuristicFidelityBestLocation
+      double costHeur = 0.;
+      double savings = 0.;
+      QMG_NOUNROLL
+      for (uint32_t i = 0; i < G1; ++i) {
+        const Gate1 e = ldGate1(gates1 + i);
+        int loc = 0;
+        double curr = 0.;
+        if (act) {
+          loc = locAfter(e.q, q1, q2, a, b);
+          curr = ldg(A.c1 + loc);
+        }
+        double best = 0.;
+        uint32_t m = g.ballot(act);
+        QMG_NOUNROLL
+        while (m != 0) {
+          const int src = ctz32(m);
+          m &= m - 1;
+          const int sLoc = g.bcast(loc, src);
+          const double sCurr = g.bcast(curr, src);
+          double v = 0.;
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
-      for (int p = g.lane; p < n; p += Group::W) {
-        const double cp = ldg(A.c1 + p);
-        if (cp >= curr) {
-          continue;
+          for (int p = g.lane; p < n; p += Group::W) {
+            const double cp = ldg(A.c1 + p);
+            if (cp >= sCurr) {
+              continue;
+            }
+            const double cur = e.mult * (sCurr - cp) - fidDist(sLoc, p, fidK);
+            v = fmax(v, cur);
+          }
+          v = gmax(g, v);
+          if (g.lane == src) {
+            best = v;
+          }
         }
-        const double cur = e.mult * (curr - cp) - fidDist(loc, p, fidK);
-        best = fmax(best, cur);
+        savings += best;
       }
-      best = gmax(g, best);
-      savings += best;
-    }
-    QMG_NOUNROLL
-    for (uint32_t i = 0; i < G; ++i) {
-      const Gate2 e = ldGate(gates + i);
-      const int l1 = locAfter(e.q1, q1, q2, a, b);
-      const int l2 = locAfter(e.q2, q1, q2, a, b);
-      double sc = DBL_MAX;
-      // the minimum over the coupling edges depends on (l1, l2) only (gate
-      // multiplicities and table index are fixed for the call): long searches
-      // meet the same pair of locations in many nodes, so the full variant
-      // keeps the value per pair - the same double, computed once
-      bool hit = false;
-      size_t slot = 0;
-      const bool memo = kFull && M.pairVal != nullptr && i < kPairGates;
-      if (memo) {
-        slot = (static_cast<size_t>(i) * n + l1) * n + l2;
-        if (M.pairTag[slot] == pairKey()) {
-          sc = M.pairVal[slot];
-          hit = true;
+      QMG_NOUNROLL
+      for (uint32_t i = 0; i < G; ++i) {
+        const Gate2 e = ldGate(gates + i);
+        int l1 = 0, l2 = 0;
+        if (act) {
+          l1 = locAfter(e.q1, q1, q2, a, b);
+          l2 = locAfter(e.q2, q1, q2, a, b);
         }
-      }
-      if (!hit) {
-        // (iterations are independent gathers: unrolled so that they overlap)
+        double sc = DBL_MAX;
+        // the minimum over the coupling edges depends on (l1, l2) only (gate
+        // multiplicities and table index are fixed for the call): long
+        // searches meet the same pair of locations in many nodes, so the full
+        // variant keeps the value per pair - the same double, computed once
+        bool hit = false;
+        size_t slot = 0;
+        const bool memo = kFull && M.pair != nullptr && i < kPairGates;
+        const uint64_t key = pairKey();
+        if (memo && act) {
+          slot = (static_cast<size_t>(i) * n + l1) * n + l2;
+          const PairSlot ps = M.pair[slot];
+          if (ps.tag == key) {
+            sc = ps.val;
+            hit = true;
+          }
+        }
+        uint32_t m = g.ballot(act && !hit);
+        QMG_NOUNROLL
+        while (m != 0) {
+          const int src = ctz32(m);
+          m &= m - 1;
+          const int s1 = g.bcast(l1, src);
+          const int s2 = g.bcast(l2, src);
+          double v = DBL_MAX;
+          // (iterations are independent gathers: unrolled so that they overlap)
 #if defined(__CUDA_ARCH__)
 #pragma unroll 3
 #endif
-        for (int k = g.lane; k < A.nE; k += Group::W) {
-          const int q3 = ldg(A.edges + 2 * k);
-          const int q4 = ldg(A.edges + 2 * k + 1);
-          const double c34 = ldg(A.c2 + q3 * n + q4);
-          const double c43 = ldg(A.c2 + q4 * n + q3);
-          const double v1 = e.fwd * c34 + e.rev * c43 + fidDist(l1, q3, fidK) +
-                            fidDist(l2, q4, fidK);
-          sc = fmin(sc, v1);
-          const double v2 = e.fwd * c43 + e.rev * c34 + fidDist(l2, q3, fidK) +
-                            fidDist(l1, q4, fidK);
-          sc = fmin(sc, v2);
-        }
-        sc = gmin(g, sc);
-        if (memo) {
-          g.sync();
-          if (g.lane == 0) {
-            M.pairVal[slot] = sc;
-            M.pairTag[slot] = pairKey();
+          for (int k = g.lane; k < A.nE; k += Group::W) {
+            const int q3 = ldg(A.edges + 2 * k);
+            const int q4 = ldg(A.edges + 2 * k + 1);
+            const double c34 = ldg(A.c2 + q3 * n + q4);
+            const double c43 = ldg(A.c2 + q4 * n + q3);
+            const double v1 = e.fwd * c34 + e.rev * c43 +
+                              fidDist(s1, q3, fidK) + fidDist(s2, q4, fidK);
+            v = fmin(v, v1);
+            const double v2 = e.fwd * c43 + e.rev * c34 +
+                              fidDist(s2, q3, fidK) + fidDist(s1, q4, fidK);
+            v = fmin(v, v2);
           }
-          g.sync();
+          v = gmin(g, v);
+          if (g.lane == src) {
+            sc = v;
+            if (memo) {
+              PairSlot ps;
+              ps.tag = key;
+              ps.val = v;
+              M.pair[slot] = ps;
+            }
+          }
+        }
+        if (act) {
+          if (adjU(l1, l2)) {
+            const double currEdge = (e.fwd * ldg(A.c2 + l1 * n + l2) +
+                                     e.rev * ldg(A.c2 + l2 * n + l1));
+            savings += (currEdge - sc);
+          } else {
+            costHeur += sc;
+          }
         }
       }
-      if (adjU(l1, l2)) {
-        const double currEdge = (e.fwd * ldg(A.c2 + l1 * n + l2) +
-                                 e.rev * ldg(A.c2 + l2 * n + l1));
-        savings += (currEdge - sc);
-      } else {
-        costHeur += sc;
+      if (act) {
+        Child& out = S.ch()[c];
+        out.fixed = fixed;
+        out.rev = 0.;
+        out.heur = costHeur - savings;
+        out.shared = 0;
+        out.nValid = static_cast<uint16_t>(nValid);
+        out.valid = (nValid == G) ? 1 : 0;
       }
+      // (memo slots written above are read by later passes of this loop)
+      g.sync();
     }
-    out.a = static_cast<uint16_t>(a < 0 ? 0 : a);
-    out.b = static_cast<uint16_t>(b < 0 ? 0 : b);
-    out.fixed = fixed;
-    out.rev = 0.;
-    out.heur = costHeur - savings;
-    out.shared = 0;
-    out.nValid = static_cast<uint16_t>(nValid);
-    out.valid = (nValid == G) ? 1 : 0;
   }
 
   // ------------------------------------------------------------------------
@@ -1476,7 +1593,9 @@ template <int H, bool kFull> struct Search {
     const uint32_t hi = lo + kBlk < nOpen ? lo + kBlk : nOpen;
     const uint32_t p = blkTopOf(c, open, lo, hi);
     if (g.lane == 0) {
-      btop[b] = open[p];
+      OpenEntry e = open[p];
+      e.hash = p;  // (block tops carry their position, not the layout hash)
+      btop[b] = e;
     }
     g.sync();
   }
@@ -1490,19 +1609,19 @@ template <int H, bool kFull> struct Search {
       blkRescan(c, open, btop, nOpen, b);
     }
   }
-  QMG_COLD static uint32_t blkTopPos(OpenCtx c, const OpenEntry* btop,
-                                     uint32_t nOpen) {
+  // the top of the open list: its entry, with the position in .hash
+  QMG_COLD static OpenEntry blkTop(OpenCtx c, const OpenEntry* btop,
+                                   uint32_t nOpen) {
     const uint32_t nb = (nOpen + kBlk - 1) / kBlk;
     const uint32_t b = blkTopOf(c, btop, 0, nb);
-    return hdrOf(c, btop[b].idx)->openPos;
+    return btop[b];
   }
-  // the entry at pos was appended (fresh: it opened a new block) or replaced
+  // the entry e at pos was appended (fresh: it opened a new block) or replaced
   // by a better one
-  QMG_COLD static void blkChanged(OpenCtx c, const OpenEntry* open,
-                                  OpenEntry* btop, uint32_t pos, bool fresh) {
+  QMG_COLD static void blkChanged(OpenCtx c, OpenEntry* btop, OpenEntry e,
+                                  uint32_t pos, bool fresh) {
     const Group g;
     if (g.lane == 0) {
-      const OpenEntry e = open[pos];
       const uint32_t b = pos / kBlk;
       bool take = fresh;
       if (!take) {
@@ -1510,6 +1629,7 @@ template <int H, bool kFull> struct Search {
         take = t.idx == e.idx || hasPriorityOf(c, e, t);
       }
       if (take) {
+        e.hash = pos;  // (block tops carry their position, not the hash)
         btop[b] = e;
       }
     }
@@ -1531,28 +1651,33 @@ template <int H, bool kFull> struct Search {
     }
   }
 
-  QMG_HD uint32_t topPos() const {
+  // the entry on top of the open list and its position
+  QMG_HD OpenEntry topEntry(uint32_t& pos) const {
     if (kFull && blockMode) {
-      return blkTopPos(octx(), M.btop, nOpen);
+      const OpenEntry e = blkTop(octx(), M.btop, nOpen);
+      pos = static_cast<uint32_t>(e.hash);
+      return e;
     }
-    return topOfS(octx(), M.open, 0, nOpen);
+    pos = topOfS(octx(), M.open, 0, nOpen);
+    return M.open[pos];
   }
 
-  QMG_HD void removeOpen(uint32_t pos) {
+  // pop: take the entry at pos (node idx, goal flag valid) off the open list
+  QMG_HD void removeOpen(uint32_t pos, uint32_t idx, bool valid) {
     // group-uniform; lane 0 writes
     const uint32_t last = nOpen - 1;
     uint32_t moved = kNone;
-    if (kFull && blockMode) {
-      moved = M.open[last].idx;
-    }
-    if (g.lane == 0) {
-      const uint32_t idx = M.open[pos].idx;
-      hdr(idx)->flags &= static_cast<uint16_t>(~2U);
-      if (pos != last) {
-        const OpenEntry e = M.open[last];
+    if (pos != last) {
+      const OpenEntry e = M.open[last];
+      moved = e.idx;
+      if (g.lane == 0) {
         M.open[pos] = e;
         hdr(e.idx)->openPos = pos;
       }
+    }
+    if (g.lane == 0) {
+      // flags: bit0 goal, bit1 open (cleared)
+      hdr(idx)->flags = static_cast<uint16_t>(valid ? 1U : 0U);
     }
     nOpen = last;
     g.sync();
@@ -1561,34 +1686,40 @@ template <int H, bool kFull> struct Search {
     }
   }
 
+  // 4 consecutive entries i0..i0+3 of "parent layout array with the entries
+  // at x and y replaced" as one little-endian 64-bit word (entries beyond n
+  // are 0)
+  QMG_HD uint64_t patchedWord(const int16_t* src, int i0, int x, int16_t vx,
+                              int y, int16_t vy) const {
+    uint64_t w = 0;
+    for (int t = 0; t < 4; ++t) {
+      const int i = i0 + t;
+      uint16_t v = 0;
+      if (i < n) {
+        v = static_cast<uint16_t>(i == x ? vx : (i == y ? vy : src[i]));
+      }
+      w |= static_cast<uint64_t>(v) << (16 * t);
+    }
+    return w;
+  }
+
   // write a node record: parent layout (pQ/pL) with the child's swap
   QMG_HD void writeNode(uint32_t idx, const Child& ch, uint32_t parentIdx,
                         uint32_t depth, uint32_t id, uint32_t openPos,
                         bool root) {
     int16_t* q = nodeQ(idx);
     int16_t* l = nodeL(idx);
-    const int a = ch.a;
-    const int b = ch.b;
-    const int q1 = root ? -2 : pQ[a];
-    const int q2 = root ? -2 : pQ[b];
+    // (root: no entry is patched)
+    const int a = root ? -1 : ch.a;
+    const int b = root ? -1 : ch.b;
+    const int q1 = root ? -2 : pQ[ch.a];
+    const int q2 = root ? -2 : pQ[ch.b];
     QMG_NOUNROLL
-    for (int i = g.lane; i < n; i += Group::W) {
-      int16_t vq = pQ[i];
-      int16_t vl = pL[i];
-      if (!root) {
-        if (i == a) {
-          vq = static_cast<int16_t>(q2);
-        } else if (i == b) {
-          vq = static_cast<int16_t>(q1);
-        }
-        if (i == q1) {
-          vl = static_cast<int16_t>(b);
-        } else if (i == q2) {
-          vl = static_cast<int16_t>(a);
-        }
-      }
-      q[i] = vq;
-      l[i] = vl;
+    for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
+      st64(q + i0, patchedWord(pQ, i0, a, static_cast<int16_t>(q2), b,
+                               static_cast<int16_t>(q1)));
+      st64(l + i0, patchedWord(pL, i0, q1, static_cast<int16_t>(b), q2,
+                               static_cast<int16_t>(a)));
     }
     if (g.lane == 0) {
       NodeHdr* h = hdr(idx);
@@ -1624,59 +1755,64 @@ template <int H, bool kFull> struct Search {
     return e;
   }
 
-  // does the stored node idx have the layout "parent with ch's swap"?
-  QMG_HD bool sameLayout(uint32_t idx, const Child& ch, bool root) const {
+  // this lane's share of comparing the stored node idx with the layout
+  // "parent with the SWAP on (a, b)" (a < 0: the parent itself): true if any
+  // of the lane's entries differ
+  QMG_HD bool layoutDiffers(uint32_t idx, int a, int b) const {
     const int16_t* q = nodeQ(idx);
-    const int a = ch.a;
-    const int b = ch.b;
+    const int16_t va = a < 0 ? static_cast<int16_t>(0) : pQ[b];
+    const int16_t vb = a < 0 ? static_cast<int16_t>(0) : pQ[a];
     bool diff = false;
     QMG_NOUNROLL
-    for (int i0 = 0; i0 < n; i0 += Group::W) {
-      const int i = i0 + g.lane;
-      if (i < n) {
-        int16_t v = pQ[i];
-        if (!root) {
-          if (i == a) {
-            v = pQ[b];
-          } else if (i == b) {
-            v = pQ[a];
-          }
-        }
-        diff = diff || (q[i] != v);
-      }
+    for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
+      // (record entries beyond n are written as 0 by writeNode)
+      diff = diff || (ld64(q + i0) != patchedWord(pQ, i0, a, va, b, vb));
     }
+    return diff;
+  }
+  // does the stored node idx have the layout "parent with ch's swap"?
+  QMG_HD bool sameLayout(uint32_t idx, const Child& ch, bool root) const {
     // (one vote for the whole layout: equal hashes almost always mean equal
     // layouts, and the loads of all iterations overlap this way)
-    return !g.any(diff);
+    return !g.any(layoutDiffers(idx, root ? -1 : ch.a, root ? -1 : ch.b));
   }
+
+  QMG_HD uint32_t homeSlot(uint64_t h) const {
+    return static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
+  }
+  QMG_HD uint32_t curStamp() const { return M.stamp & kStampMask; }
 
   // switch from scanning the open list to the layout-keyed hash table
   QMG_HD void buildTable() {
     g.sync();
     if (g.lane == 0) {
+      const uint32_t cur = curStamp();
       QMG_NOUNROLL
       for (uint32_t i = 0; i < nOpen; ++i) {
         const OpenEntry e = M.open[i];
-        uint32_t slot = static_cast<uint32_t>(e.hash ^ (e.hash >> 32)) &
-                        M.tableMask;
+        uint32_t slot = homeSlot(e.hash);
         QMG_NOUNROLL
-        while (static_cast<uint32_t>(M.table[slot] >> 32) == M.stamp) {
+        while (tabStamp(M.table[slot]) == cur) {
           slot = (slot + 1) & M.tableMask;
         }
-        M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | e.idx;
+        M.table[slot] = tabPack(cur, e.hash, e.idx);
       }
     }
     tableMode = true;
     g.sync();
   }
 
-  // UniquePriorityQueue::push :59-82.  Group-uniform.  Returns false when the
-  // node pool is exhausted.  Only nodes in the open list take part in the
-  // layout identity (pop erases the membership, :84-93), so short open lists
-  // are scanned directly; longer ones are indexed by the hash table.
+  // UniquePriorityQueue::push :59-82 for one node.  Group-uniform.  Returns
+  // false when the node pool is exhausted.  Only nodes in the open list take
+  // part in the layout identity (pop erases the membership, :84-93), so short
+  // open lists are scanned directly; longer ones are indexed by the hash table.
   QMG_HD bool push(const Child& ch, uint32_t parentIdx, uint32_t depth,
                    bool root) {
     const uint32_t id = nextId++;
+    return pushOne(ch, parentIdx, depth, root, id);
+  }
+  QMG_HD bool pushOne(const Child& ch, uint32_t parentIdx, uint32_t depth,
+                      bool root, uint32_t id) {
     const uint64_t h = ch.hash;
     uint32_t found = kNone;  // pool index of an OPEN node with this layout
     uint32_t slot = 0;
@@ -1699,14 +1835,15 @@ template <int H, bool kFull> struct Search {
         }
       }
     } else {
-      slot = static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
+      const uint32_t cur = curStamp();
+      slot = homeSlot(h);
       for (;;) {
         const uint64_t e = M.table[slot];
-        if (static_cast<uint32_t>(e >> 32) != M.stamp) {
+        if (tabStamp(e) != cur) {
           break;  // free slot
         }
-        const uint32_t idx = static_cast<uint32_t>(e);
-        if (hdr(idx)->hash == h && sameLayout(idx, ch, root)) {
+        const uint32_t idx = tabIdx(e);
+        if (tabHashEq(e, h) && idx < nPool && sameLayout(idx, ch, root)) {
           found = idx;
           break;
         }
@@ -1731,7 +1868,7 @@ template <int H, bool kFull> struct Search {
         }
         g.sync();
         if (kFull && blockMode) {
-          blkChanged(octx(), M.open, M.btop, pos, false);
+          blkChanged(octx(), M.btop, ne, pos, false);
         }
       }
       return true;
@@ -1742,15 +1879,198 @@ template <int H, bool kFull> struct Search {
     const uint32_t idx = nPool++;
     const uint32_t pos = nOpen++;
     writeNode(idx, ch, parentIdx, depth, id, pos, root);
+    const OpenEntry ne = entryOf(ch, idx);
     if (g.lane == 0) {
-      M.open[pos] = entryOf(ch, idx);
+      M.open[pos] = ne;
       if (tableMode) {
-        M.table[slot] = (static_cast<uint64_t>(M.stamp) << 32) | idx;
+        M.table[slot] = tabPack(curStamp(), h, idx);
       }
     }
     g.sync();
     if (kFull && blockMode) {
-      blkChanged(octx(), M.open, M.btop, pos, pos % kBlk == 0);
+      blkChanged(octx(), M.btop, ne, pos, pos % kBlk == 0);
+    }
+    return true;
+  }
+
+  // push() for the cnt children in S.ch() of one parent, long open lists
+  // (hash-table mode): the look-ups - table probe, layout comparison, the
+  // record of an open duplicate - are done for all children at once, ONE CHILD
+  // PER LANE, so that their memory latencies overlap; the children are then
+  // committed one after the other in generation order, which keeps node ids,
+  // pool and open-list positions exactly as push() child by child gives them.
+  // Siblings that could see each other's insertion (equal layout hash, or the
+  // same free table slot) take the one-by-one path at their turn.
+  QMG_HD bool pushChunk(int cnt, uint32_t parentIdx, uint32_t depth) {
+    const uint32_t cur = curStamp();
+    enum : uint32_t { kSkip = 0, kReplace = 1, kNew = 2, kSlow = 3 };
+    QMG_NOUNROLL
+    for (int c0 = 0; c0 < cnt; c0 += Group::W) {
+      const int c = c0 + g.lane;
+      const bool act = c < cnt;
+      uint64_t h = 0;
+      int a = 0, b = 0;
+      if (act) {
+        h = S.ch()[c].hash;
+        a = S.ch()[c].a;
+        b = S.ch()[c].b;
+      }
+      uint32_t slot = homeSlot(h);
+      uint32_t found = kNone;
+      bool done = !act;
+      // ---- look-up: probe to the next candidate, confirm candidates by
+      // comparing layouts (the whole group per candidate, several in flight)
+      QMG_NOUNROLL
+      for (;;) {
+        uint32_t cand = kNone;
+        if (!done) {
+          QMG_NOUNROLL
+          for (;;) {
+            const uint64_t e = M.table[slot];
+            if (tabStamp(e) != cur) {
+              done = true;  // free slot: not in the table
+              break;
+            }
+            if (tabHashEq(e, h) && tabIdx(e) < nPool) {
+              cand = tabIdx(e);
+              break;
+            }
+            slot = (slot + 1) & M.tableMask;
+          }
+        }
+        uint32_t m = g.ballot(cand != kNone);
+        if (m == 0) {
+          break;
+        }
+        QMG_NOUNROLL
+        while (m != 0) {
+          constexpr int kFlight = 4;
+          int src[kFlight];
+          bool diff[kFlight];
+          for (int k = 0; k < kFlight; ++k) {
+            src[k] = -1;
+            if (m != 0) {
+              src[k] = ctz32(m);
+              m &= m - 1;
+            }
+          }
+          for (int k = 0; k < kFlight; ++k) {
+            diff[k] = false;
+            if (src[k] >= 0) {
+              diff[k] = layoutDiffers(g.bcast(cand, src[k]), g.bcast(a, src[k]),
+                                      g.bcast(b, src[k]));
+            }
+          }
+          for (int k = 0; k < kFlight; ++k) {
+            if (src[k] >= 0) {
+              const bool same = !g.any(diff[k]);
+              if (g.lane == src[k]) {
+                if (same) {
+                  found = cand;
+                  done = true;
+                } else {
+                  slot = (slot + 1) & M.tableMask;
+                }
+              }
+            }
+          }
+        }
+      }
+      // ---- what happens to the child, from the duplicate's record
+      uint32_t dec = kSkip;
+      uint32_t pos = 0;
+      bool freeSlot = false;
+      if (act) {
+        dec = kNew;
+        freeSlot = found == kNone;
+        if (found != kNone) {
+          const NodeHdr* hf = hdr(found);
+          const uint32_t fl = hf->flags;
+          // (closed: the slot is re-pointed to the new node)
+          if ((fl & 2U) != 0) {
+            // the open-list keys of the duplicate, as entryOf() made them
+            OpenEntry ex;
+            ex.f = hf->fixed + hf->rev + hf->heur + hf->look;
+            ex.h2 = hf->heur + hf->look;
+            ex.hash = 0;
+            ex.idx = found;
+            ex.nValid = hf->nValid;
+            ex.valid = static_cast<uint16_t>(fl & 1U);
+            pos = hf->openPos;
+            dec = cmp4(entryOf(S.ch()[c], found), ex) < 0 ? kReplace : kSkip;
+          }
+        }
+      }
+      // ---- siblings that may interact: equal hashes, or two new nodes that
+      // found the same free slot
+      const uint32_t below = g.lane == 0 ? 0U : (0xffffffffU >> (32 - g.lane));
+      {
+        const uint32_t same = g.matchAny(act, h);
+        if ((same & below) != 0) {
+          dec = kSlow;
+        }
+        const bool wantsFree = act && dec == kNew && freeSlot;
+        const uint32_t sameSlot = g.matchAny(wantsFree, static_cast<uint64_t>(slot));
+        if (wantsFree && (sameSlot & below) != 0) {
+          dec = kSlow;
+        }
+      }
+      // ---- commit in generation order
+      bool reprobe = false;
+      const int nj = (cnt - c0) < Group::W ? (cnt - c0) : Group::W;
+      QMG_NOUNROLL
+      for (int j = 0; j < nj; ++j) {
+        const Child ch = S.ch()[c0 + j];
+        const uint32_t id = nextId++;
+        const uint32_t d = g.bcast(dec, j);
+        if (d == kSkip) {
+          continue;
+        }
+        if (d == kSlow) {
+          if (!pushOne(ch, parentIdx, depth, false, id)) {
+            return false;
+          }
+          reprobe = true;  // it may have taken a free slot a later sibling holds
+          continue;
+        }
+        if (d == kReplace) {
+          const uint32_t fidx = g.bcast(found, j);
+          const uint32_t fpos = g.bcast(pos, j);
+          g.sync();
+          writeNode(fidx, ch, parentIdx, depth, id, fpos, false);
+          const OpenEntry ne = entryOf(ch, fidx);
+          if (g.lane == 0) {
+            M.open[fpos] = ne;
+          }
+          g.sync();
+          if (blockMode) {
+            blkChanged(octx(), M.btop, ne, fpos, false);
+          }
+          continue;
+        }
+        if (nPool >= M.poolCap) {
+          return false;
+        }
+        uint32_t sl = g.bcast(slot, j);
+        if (reprobe && g.bcast(freeSlot, j)) {
+          QMG_NOUNROLL
+          while (tabStamp(M.table[sl]) == cur) {
+            sl = (sl + 1) & M.tableMask;
+          }
+        }
+        const uint32_t idx = nPool++;
+        const uint32_t npos = nOpen++;
+        writeNode(idx, ch, parentIdx, depth, id, npos, false);
+        const OpenEntry ne = entryOf(ch, idx);
+        if (g.lane == 0) {
+          M.open[npos] = ne;
+          M.table[sl] = tabPack(cur, ch.hash, idx);
+        }
+        g.sync();
+        if (blockMode) {
+          blkChanged(octx(), M.btop, ne, npos, npos % kBlk == 0);
+        }
+      }
     }
     return true;
   }
@@ -1761,19 +2081,7 @@ template <int H, bool kFull> struct Search {
                        uint64_t parentHash) {
     g.sync();
     if (kFid) {
-      QMG_NOUNROLL
-      for (int c = 0; c < cnt; ++c) {
-        Child out;
-        scoreFidelity(root ? 0 : S.ch()[c].a, root ? 0 : S.ch()[c].b, pc, out);
-        if (g.lane == 0) {
-          S.ch()[c].fixed = out.fixed;
-          S.ch()[c].rev = out.rev;
-          S.ch()[c].heur = out.heur;
-          S.ch()[c].shared = 0;
-          S.ch()[c].nValid = out.nValid;
-          S.ch()[c].valid = out.valid;
-        }
-      }
+      scoreFidelityChunk(cnt, root, pc);
     } else {
       QMG_NOUNROLL
       for (int c = g.lane; c < cnt; c += Group::W) {
@@ -2083,6 +2391,18 @@ template <int H, bool kFull> struct Search {
       M.epoch = M.epoch + 1 < kMaxEpochs ? M.epoch + 1 : kMaxEpochs - 1;
     }
     g.sync();
+    if (!resume && (M.stamp & kStampMask) == 0) {
+      // the 24 stamp bits of the table entries wrapped: forget every entry
+      QMG_NOUNROLL
+      for (uint32_t i = g.lane; i <= M.tableMask; i += Group::W) {
+        M.table[i] = 0;
+      }
+      g.sync();
+      if (g.lane == 0) {
+        ++M.stamp;
+      }
+      g.sync();
+    }
     if (kFull && g.lane == 0) {
       M.childExtra = 0;
       if (M.priv != nullptr) {
@@ -2152,11 +2472,17 @@ template <int H, bool kFull> struct Search {
           }
           g.sync();
         }
-        QMG_NOUNROLL
-        for (int c = 0; c < cnt; ++c) {
-          const Child ch = S.ch()[c];
-          if (!push(ch, parent, depth, rootMode)) {
+        if (kFull && tableMode && !rootMode) {
+          if (!pushChunk(cnt, parent, depth)) {
             return ST_POOL;
+          }
+        } else {
+          QMG_NOUNROLL
+          for (int c = 0; c < cnt; ++c) {
+            const Child ch = S.ch()[c];
+            if (!push(ch, parent, depth, rootMode)) {
+              return ST_POOL;
+            }
           }
         }
       }
@@ -2209,8 +2535,8 @@ template <int H, bool kFull> struct Search {
         blkEnter(octx(), M.open, M.btop, nOpen);
         blockMode = true;
       }
-      const uint32_t pos = topPos();
-      const OpenEntry top = M.open[pos];
+      uint32_t pos = 0;
+      const OpenEntry top = topEntry(pos);
       if (found && !(top.f < bestFixedTotal)) {
         break;
       }
@@ -2235,7 +2561,7 @@ template <int H, bool kFull> struct Search {
           break;
         }
       }
-      removeOpen(pos);
+      removeOpen(pos, cur, top.valid != 0);
       // ---- stage the node to expand
       if (!maskReady) {
         buildMask();

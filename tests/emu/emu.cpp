@@ -137,8 +137,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
   while (tableSize < 2 * poolNodes) {
     tableSize <<= 1;
   }
-  const uint32_t recBytes =
-      static_cast<uint32_t>((sizeof(NodeHdr) + 4U * n + 7U) & ~7U);
+  const uint32_t recBytes = nodeRecBytes(n);
   std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8);
   std::vector<OpenEntry> open(poolNodes);
   std::vector<uint64_t> table(tableSize, 0);
@@ -207,14 +206,11 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     M.table = table.data();
     std::vector<OpenEntry> btop(poolNodes / kBlk + 2);
     M.btop = btop.data();
-    std::vector<double> pairVal;
-    std::vector<uint64_t> pairTag;
+    std::vector<PairSlot> pair;
     if (C.heuristic >= 4) {
       const size_t slots = static_cast<size_t>(kPairGates) * A.n * A.n;
-      pairVal.assign(slots, 0.);
-      pairTag.assign(slots, 0);
-      M.pairVal = pairVal.data();
-      M.pairTag = pairTag.data();
+      pair.assign(slots, PairSlot{0, 0.});
+      M.pair = pair.data();
     }
     M.nsw = nsw.data();
     M.poolCap = poolNodes;

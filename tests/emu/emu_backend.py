@@ -34,8 +34,11 @@ def build(asan: bool = False) -> str:
     flags = ["-std=c++17", "-fPIC", "-shared", "-Wall", "-Wextra", "-g"]
     flags += ["-O1", "-fsanitize=address,undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
     if blk:
-        b, bmin = blk.split(",")
-        flags += [f"-DQMG_BLK={int(b)}", f"-DQMG_BLK_MIN={int(bmin)}"]
+        # "4,8,2": in addition the layout hash table from 3 open nodes on
+        parts = blk.split(",")
+        flags += [f"-DQMG_BLK={int(parts[0])}", f"-DQMG_BLK_MIN={int(parts[1])}"]
+        if len(parts) > 2:
+            flags += [f"-DQMG_SCAN_MAX={int(parts[2])}"]
     subprocess.check_call([cxx, *flags, "-o", out, src])
     return out
 

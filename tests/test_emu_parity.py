@@ -134,6 +134,8 @@ def test_random_circuits_with_layer_splits_against_oracle(arch, calib):
 
 
 @pytest.mark.parametrize("env", [{"QMG_EMU_BLK": "4,8"}, {"QMG_EMU_BLK": "7,1"},
+                                 {"QMG_EMU_BLK": "4,8,2", "QMG_EMU_START_FULL": "1"},
+                                 {"QMG_EMU_BLK": "512,4096,1", "QMG_EMU_START_FULL": "1"},
                                  {"QMG_EMU_START_FULL": "1"}])
 def test_full_search_variant_matches_reference_outputs(env):
     """The kernel routes an instance with the lean search variant and again
