@@ -152,6 +152,31 @@ int qmg_build_edge_skip_table(uint16_t n, const uint16_t* edges, size_t nEdges,
                               size_t* nTables, int device);
 
 /*
+ * qmg_build_table_static: qmg_build_table (exact_association = 0, the blocked
+ * Floyd-Warshall kernel) for callers that cannot allocate.  It has NO
+ * COUNTERPART IN THE REFERENCE and was added:
+ * code under CUDA graph capture, tight serving loops and harnesses
+ * that forbid cudaMalloc need an entry point that allocates nothing.
+ *
+ * dEdges (2 * nEdges uint16), dEdgeWeights (n * n doubles, row-major) and
+ * dDistanceTable (n * n doubles, output) are DEVICE pointers on `device`; the
+ * kernels are queued on `stream` (a cudaStream_t; NULL = the default stream)
+ * and the call returns without waiting for them.  The call makes no
+ * cudaMalloc / cudaFree and uses no allocating library routine: the padded
+ * matrix the kernels work on is a static device array inside the library
+ * (QMG_STATIC_TABLE_MAX_QUBITS^2 doubles = 2 MiB, held by every GPU that loads
+ * the library until the process exits).  n above QMG_STATIC_TABLE_MAX_QUBITS
+ * is rejected with QMG_BAD_ARG.  All calls share that array: a call rewrites
+ * every cell it reads, so earlier contents never matter, but calls whose
+ * kernels overlap on one GPU (different streams or threads) race on it -
+ * serialise them.  The result equals qmg_build_table(..., 0, ...) bit for bit.
+ */
+#define QMG_STATIC_TABLE_MAX_QUBITS 512
+int qmg_build_table_static(uint16_t n, const uint16_t* dEdges, size_t nEdges,
+                           const double* dEdgeWeights, double* dDistanceTable,
+                           int device, void* stream);
+
+/*
  * Architecture handle: the device-resident form of class Architecture
  * (include/sc/Architecture.hpp:42).  qmg_arch_create replaces
  * Architecture::createDistanceTable (src/sc/Architecture.cpp:201-230);

@@ -11,7 +11,9 @@
 #include <cstdio>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <numeric>
+#include <string>
 #include <tuple>
 #include <vector>
 
@@ -346,6 +348,131 @@ QMG_API int qmg_build_edge_skip_table(uint16_t n, const uint16_t* edges,
     }
     return static_cast<int>(QMG_OK);
   });
+}
+
+// ==========================================================================
+// Table build without any allocation (no counterpart in the reference; added
+// for callers that cannot call
+// cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  The Floyd-Warshall kernels (K1) need one padded np x np matrix of
+// scratch; here it is a file-scope device array of fixed size that every GPU
+// loading the library holds until exit.
+// ==========================================================================
+namespace {
+
+constexpr int kStaticMaxQubits = QMG_STATIC_TABLE_MAX_QUBITS;  // qmap_b200.h
+static_assert(kStaticMaxQubits % kFwTile == 0, "padded size");
+// 512 x 512 doubles = 2 MiB per device.  Shared by all calls: a call rewrites
+// every cell it reads (fw_static_init), so nothing has to be cleared, but two
+// calls whose kernels overlap on one GPU would race on it.
+static __device__ __align__(256) double
+    gStaticFwScratch[static_cast<size_t>(kStaticMaxQubits) * kStaticMaxQubits];
+
+// padded matrix: 0 on the diagonal, +inf elsewhere
+__global__ void fw_static_init(double* __restrict__ d, int np) {
+  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= static_cast<size_t>(np) * np) {
+    return;
+  }
+  const int r = static_cast<int>(idx / np);
+  const int c = static_cast<int>(idx % np);
+  d[idx] = (r == c) ? 0. : __longlong_as_double(0x7ff0000000000000LL);
+}
+// both directions of every coupling entry get their weight (the undirected
+// view of utils.cpp:67-73); entries out of range are ignored
+__global__ void fw_static_edges(double* __restrict__ d, int np, int n,
+                                const uint16_t* __restrict__ edges,
+                                size_t nEdges, const double* __restrict__ w) {
+  const size_t e = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (e >= nEdges) {
+    return;
+  }
+  const int a = edges[2 * e];
+  const int b = edges[2 * e + 1];
+  if (a >= n || b >= n || a == b) {
+    return;
+  }
+  d[static_cast<size_t>(a) * np + b] = w[static_cast<size_t>(a) * n + b];
+  d[static_cast<size_t>(b) * np + a] = w[static_cast<size_t>(b) * n + a];
+}
+
+constexpr int kMaxDevices = 64;
+std::mutex gStaticMutex;
+double* gStaticScratchAddr[kMaxDevices] = {};
+
+// the device address of the scratch array on `device` (which is current);
+// looked up once per device - in host code the array's name is only a
+// stand-in, never a device address
+int staticScratch(int device, double** out) {
+  if (device < 0 || device >= kMaxDevices) {
+    return fail(QMG_BAD_ARG, "device index out of range");
+  }
+  std::lock_guard<std::mutex> lk(gStaticMutex);
+  if (gStaticScratchAddr[device] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, gStaticFwScratch);
+    if (e != cudaSuccess || p == nullptr) {
+      cudaGetLastError();
+      return fail(QMG_CUDA_ERROR, std::string("cudaGetSymbolAddress: ") +
+                                      cudaGetErrorString(e));
+    }
+    gStaticScratchAddr[device] = static_cast<double*>(p);
+  }
+  *out = gStaticScratchAddr[device];
+  return QMG_OK;
+}
+
+}  // namespace
+
+QMG_API int qmg_build_table_static(uint16_t n, const uint16_t* dEdges,
+                                   size_t nEdges, const double* dEdgeWeights,
+                                   double* dDistanceTable, int device,
+                                   void* stream) {
+  if (n > kStaticMaxQubits) {
+    return fail(QMG_BAD_ARG,
+                "qmg_build_table_static: n = " + std::to_string(n) +
+                    " exceeds the static scratch (at most " +
+                    std::to_string(kStaticMaxQubits) +
+                    " qubits); use qmg_build_table");
+  }
+  if ((nEdges > 0 && dEdges == nullptr) ||
+      (n > 0 && (dEdgeWeights == nullptr || dDistanceTable == nullptr))) {
+    return fail(QMG_BAD_ARG, "null argument");
+  }
+  if (int rc = selectDevice(device)) {
+    return rc;
+  }
+  if (n == 0) {
+    return QMG_OK;
+  }
+  double* pad = nullptr;
+  if (int rc = staticScratch(device, &pad)) {
+    return rc;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int nb = (n + kFwTile - 1) / kFwTile;
+  const int np = nb * kFwTile;
+  const size_t tot = static_cast<size_t>(np) * np;
+  fw_static_init<<<static_cast<unsigned>((tot + 255) / 256), 256, 0, s>>>(pad,
+                                                                          np);
+  if (nEdges > 0) {
+    fw_static_edges<<<static_cast<unsigned>((nEdges + 255) / 256), 256, 0, s>>>(
+        pad, np, n, dEdges, nEdges, dEdgeWeights);
+  }
+  for (int kb = 0; kb < nb; ++kb) {
+    fw_phase1<<<1, 256, 0, s>>>(pad, np, kb);
+    if (nb > 1) {
+      fw_phase2<<<dim3(nb - 1, 2), 256, 0, s>>>(pad, np, kb);
+      fw_phase3<<<dim3(nb - 1, nb - 1), 256, 0, s>>>(pad, np, kb);
+    }
+  }
+  fw_finish<<<static_cast<unsigned>((static_cast<size_t>(n) * n + 255) / 256),
+              256, 0, s>>>(pad, np, n, dDistanceTable);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    return fail(QMG_CUDA_ERROR, cudaGetErrorString(e));
+  }
+  return QMG_OK;
 }
 
 // ==========================================================================

@@ -136,7 +136,7 @@ EXPORTS = [
     "qmg_circuit_layers", "qmg_circuit_layer_gates", "qmg_circuit_layer_splittable",
     "qmg_circuit_split_layer", "qmg_circuit_destroy", "qmg_route_batch",
     "qmg_batch_create", "qmg_batch_run", "qmg_batch_fetch", "qmg_batch_destroy",
-    "qmg_last_error", "qmg_device_count", "qmg_version",
+    "qmg_last_error", "qmg_device_count", "qmg_version", "qmg_build_table_static",
 ]
 
 _lib = None
@@ -172,6 +172,7 @@ def load(path: str = LIB_PATH):
     L.qmg_version.restype = C.c_char_p
     L.qmg_device_count.restype = C.c_int
     L.qmg_build_table.argtypes = [u16, vp, sz, vp, i32, vp, i32]
+    L.qmg_build_table_static.argtypes = [u16, vp, sz, vp, vp, i32, vp]
     L.qmg_build_single_edge_skip_table.argtypes = [u16, vp, vp, sz, dbl, vp, i32]
     L.qmg_build_edge_skip_table.argtypes = [u16, vp, sz, vp, i32, vp, sz,
                                             C.POINTER(C.c_size_t), i32]
