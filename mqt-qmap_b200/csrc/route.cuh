@@ -27,6 +27,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32,
   const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
   Scratch S = lay;
   S.base = smem + static_cast<size_t>(warp) * lay.bytes;
+  // the layout arrays are moved as 64-bit words: their entries beyond n must
+  // be zero (they are never written afterwards)
+  for (uint32_t w = kOffVar / 4 + lane; w < lay.bytes / 4; w += 32) {
+    reinterpret_cast<uint32_t*>(S.base)[w] = 0;
+  }
   // the warp-uniform descriptors are kept in shared memory, not in registers
   InstView* sI = S.inst();
   SearchMem* sM = S.mem();

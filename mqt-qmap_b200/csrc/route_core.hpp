@@ -1686,40 +1686,36 @@ template <int H, bool kFull> struct Search {
     }
   }
 
-  // 4 consecutive entries i0..i0+3 of "parent layout array with the entries
-  // at x and y replaced" as one little-endian 64-bit word (entries beyond n
-  // are 0)
-  QMG_HD uint64_t patchedWord(const int16_t* src, int i0, int x, int16_t vx,
-                              int y, int16_t vy) const {
-    uint64_t w = 0;
-    for (int t = 0; t < 4; ++t) {
-      const int i = i0 + t;
-      uint16_t v = 0;
-      if (i < n) {
-        v = static_cast<uint16_t>(i == x ? vx : (i == y ? vy : src[i]));
-      }
-      w |= static_cast<uint64_t>(v) << (16 * t);
-    }
-    return w;
-  }
-
-  // write a node record: parent layout (pQ/pL) with the child's swap
+  // write a node record: parent layout (pQ/pL) with the child's swap.  The
+  // parent's arrays are copied as 64-bit words (the scratch arrays are 8-byte
+  // aligned and zero beyond n), then the four entries the SWAP changes are
+  // stored individually.
   QMG_HD void writeNode(uint32_t idx, const Child& ch, uint32_t parentIdx,
                         uint32_t depth, uint32_t id, uint32_t openPos,
                         bool root) {
     int16_t* q = nodeQ(idx);
     int16_t* l = nodeL(idx);
-    // (root: no entry is patched)
-    const int a = root ? -1 : ch.a;
-    const int b = root ? -1 : ch.b;
-    const int q1 = root ? -2 : pQ[ch.a];
-    const int q2 = root ? -2 : pQ[ch.b];
     QMG_NOUNROLL
     for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
-      st64(q + i0, patchedWord(pQ, i0, a, static_cast<int16_t>(q2), b,
-                               static_cast<int16_t>(q1)));
-      st64(l + i0, patchedWord(pL, i0, q1, static_cast<int16_t>(b), q2,
-                               static_cast<int16_t>(a)));
+      st64(q + i0, ld64(pQ + i0));
+      st64(l + i0, ld64(pL + i0));
+    }
+    if (!root) {
+      g.sync();  // (orders the word stores before the entry stores)
+      const int a = ch.a;
+      const int b = ch.b;
+      const int q1 = pQ[a];
+      const int q2 = pQ[b];
+      if (g.lane == 0) {
+        q[a] = static_cast<int16_t>(q2);
+        q[b] = static_cast<int16_t>(q1);
+        if (q1 >= 0) {
+          l[q1] = static_cast<int16_t>(b);
+        }
+        if (q2 >= 0) {
+          l[q2] = static_cast<int16_t>(a);
+        }
+      }
     }
     if (g.lane == 0) {
       NodeHdr* h = hdr(idx);
@@ -1757,16 +1753,34 @@ template <int H, bool kFull> struct Search {
 
   // this lane's share of comparing the stored node idx with the layout
   // "parent with the SWAP on (a, b)" (a < 0: the parent itself): true if any
-  // of the lane's entries differ
+  // of the lane's entries differ.  Word by word: stored XOR parent must be 0
+  // except at the entries a and b, where it must be pQ[a] XOR pQ[b].
   QMG_HD bool layoutDiffers(uint32_t idx, int a, int b) const {
     const int16_t* q = nodeQ(idx);
-    const int16_t va = a < 0 ? static_cast<int16_t>(0) : pQ[b];
-    const int16_t vb = a < 0 ? static_cast<int16_t>(0) : pQ[a];
+    uint32_t d = 0;
+    if (a >= 0) {
+      d = (static_cast<uint32_t>(static_cast<uint16_t>(pQ[a])) ^
+           static_cast<uint32_t>(static_cast<uint16_t>(pQ[b])));
+    }
     bool diff = false;
     QMG_NOUNROLL
     for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
-      // (record entries beyond n are written as 0 by writeNode)
-      diff = diff || (ld64(q + i0) != patchedWord(pQ, i0, a, va, b, vb));
+      const uint64_t x = ld64(q + i0) ^ ld64(pQ + i0);
+      uint32_t lo = static_cast<uint32_t>(x);
+      uint32_t hi = static_cast<uint32_t>(x >> 32);
+      const uint32_t da = static_cast<uint32_t>(a - i0);
+      const uint32_t db = static_cast<uint32_t>(b - i0);
+      if (a >= 0 && da < 4U) {
+        const uint32_t v = d << ((da & 1U) << 4);
+        lo ^= (da & 2U) ? 0U : v;
+        hi ^= (da & 2U) ? v : 0U;
+      }
+      if (a >= 0 && db < 4U) {
+        const uint32_t v = d << ((db & 1U) << 4);
+        lo ^= (db & 2U) ? 0U : v;
+        hi ^= (db & 2U) ? v : 0U;
+      }
+      diff = diff || ((lo | hi) != 0U);
     }
     return diff;
   }
