@@ -265,6 +265,25 @@ int qmg_circuit_layer_splittable(const qmg_circuit* circ, uint32_t layer);
 int qmg_circuit_split_layer(qmg_circuit* circ, uint32_t layer);
 void qmg_circuit_destroy(qmg_circuit* circ);
 
+/*
+ * Mapper::createLayers (src/sc/Mapper.cpp:138-281) for a batch of circuits at
+ * once, on the host's threads, producing only the CSR layers a routing batch
+ * reads (no per-layer containers; layers of such a circuit cannot be split by
+ * qmg_circuit_split_layer - the library splits them itself when the instance
+ * has a layer_capacity).  Circuit i is the gates gateOffsets[i] ..
+ * gateOffsets[i+1] of control / target (control < 0 = single-qubit gate).
+ * The views stay valid until the batch is destroyed.
+ */
+typedef struct qmg_circuit_batch qmg_circuit_batch;
+int qmg_circuit_batch_create(uint32_t nArchQubits, size_t nCircuits,
+                             const uint64_t* gateOffsets,
+                             const int32_t* control, const int32_t* target,
+                             int32_t layering /* qmg_layering */,
+                             qmg_circuit_batch** out);
+int qmg_circuit_batch_layers(const qmg_circuit_batch* batch, size_t i,
+                             qmg_layers* out);
+void qmg_circuit_batch_destroy(qmg_circuit_batch* batch);
+
 /* one search unit: a circuit, a start layout and a pass schedule */
 typedef struct {
   qmg_layers layers;
@@ -289,6 +308,15 @@ typedef struct {
    * split is handed to the caller as QMG_SPLIT_LIMIT_HIT. */
   uint32_t layer_capacity;
 } qmg_instance;
+
+/* instances[i].layers = the layers of circuit i for i < nInstances (the other
+ * fields are left as they are) */
+int qmg_circuit_batch_fill_instances(const qmg_circuit_batch* batch,
+                                     qmg_instance* instances,
+                                     size_t nInstances);
+/* gate indices of every layer of circuit i (as qmg_circuit_layer_gates) */
+int qmg_circuit_batch_layer_gates(const qmg_circuit_batch* batch, size_t i,
+                                  uint32_t* offsets, uint32_t* gateIndices);
 
 /* result of one aStarMap call (HeuristicMapper::Node + the counters of
  * MappingResults::LayerHeuristicBenchmarkInfo, include/sc/MappingResults.hpp:
@@ -355,7 +383,34 @@ typedef struct {
   uint32_t* split_layers; /* capacity split_capacity, or NULL */
   uint32_t split_capacity;
   uint32_t n_splits;
+  /* the final routing pass alone: what the reference reports as
+   * heuristicBenchmark.expandedNodes / generatedNodes (its counters are off
+   * during pseudoRouteCircuit, HeuristicMapper.cpp:309-344) */
+  uint64_t expanded_nodes_final_pass;
+  uint64_t generated_nodes_final_pass;
 } qmg_route_result;
+
+/*
+ * Replay check of routed instances (the reference delegates circuit
+ * equivalence to mqt.qcec, test/python/test_heuristic_mapper.py:29-81, which
+ * is not part of it): for instance i, starting from results[i].start_locations,
+ * the SWAPs of every layer must sit on coupling edges, after them every 2q gate
+ * of the layer must act on adjacent physical qubits (placements are consumed in
+ * order for qubits placed on the way) and the layout reached must equal
+ * final_locations - i.e. the routed circuit is the input circuit under the
+ * SWAP-induced permutation.  verdict[i]: 1 valid, 0 invalid, 2 not checkable
+ * (instance not finished, layers split by the library, outputs missing).
+ * Host only.
+ */
+int qmg_circuit_batch_verify(const qmg_circuit_batch* batch, uint16_t n,
+                             const uint16_t* edges, size_t nEdges,
+                             const uint64_t* gateOffsets,
+                             const int32_t* control, const int32_t* target,
+                             const qmg_route_result* results,
+                             size_t nInstances,
+                             int32_t fidelityAware /* heuristic is
+                             fidelity_best_location: 1q gates place qubits */,
+                             uint8_t* verdict);
 
 typedef struct {
   uint32_t pool_nodes;       /* node-pool capacity per resident search, 0=auto */

@@ -343,7 +343,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   Layout lo;
   b->oSwapCounter = lo.add(16);  // [0] packed-SWAP counter, [1] ticket
   b->oSummary = lo.add(nInst * 8 * 4);
-  b->oCounters = lo.add(nInst * 2 * 8);
+  b->oCounters = lo.add(nInst * 4 * 8);
   b->oFinalQ = lo.add(nInst * n * 2);
   b->oFinalL = lo.add(nInst * n * 2);
   b->oStartL = lo.add(nInst * n * 2);
@@ -561,7 +561,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.finalL = at<int16_t>(O, b->oFinalL) + i * n;
     I.startL = at<int16_t>(O, b->oStartL) + i * n;
     I.summary = at<uint32_t>(O, b->oSummary) + 8 * i;
-    I.counters = at<uint64_t>(O, b->oCounters) + 2 * i;
+    I.counters = at<uint64_t>(O, b->oCounters) + 4 * i;
   });
   if (badInit.load() != 0) {
     return fail(QMG_BAD_ARG, badInit.load() == 2
@@ -740,8 +740,10 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
                   static_cast<size_t>(k) * 4);
     }
     r.status = static_cast<int32_t>(summary[8 * i + 3]);
-    r.expanded_nodes = counters[2 * i];
-    r.generated_nodes = counters[2 * i + 1];
+    r.expanded_nodes = counters[4 * i];
+    r.generated_nodes = counters[4 * i + 1];
+    r.expanded_nodes_final_pass = counters[4 * i + 2];
+    r.generated_nodes_final_pass = counters[4 * i + 3];
     exp.fetch_add(r.expanded_nodes, std::memory_order_relaxed);
     gen.fetch_add(r.generated_nodes, std::memory_order_relaxed);
     const size_t nl = std::min(

@@ -4,11 +4,15 @@
 #pragma once
 #include <cstring>
 #include <exception>
+#include <atomic>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
 #include "../../include/qmap_b200.h"
+#include "flat_layers.hpp"
+#include "flatten.hpp"
 #include "layers.hpp"
 
 namespace qmg {
@@ -75,6 +79,11 @@ struct qmg_circuit {
   qmg::LayeredCircuit lc;
   qmg::FlatCircuit flat;  // with the 1q gates of every layer (fidelity view)
   void reflatten() { flat.fromLayered(lc, true); }
+};
+
+// createLayers of many circuits at once, CSR only (flat_layers.hpp)
+struct qmg_circuit_batch {
+  std::vector<qmg::FlatLayers> circ;
 };
 
 #define QMG_API extern "C" __attribute__((visibility("default")))
@@ -156,4 +165,209 @@ QMG_API int qmg_circuit_split_layer(qmg_circuit* c, uint32_t layer) {
   return QMG_OK;
 }
 QMG_API void qmg_circuit_destroy(qmg_circuit* c) { delete c; }
+
+QMG_API int qmg_circuit_batch_create(uint32_t nArchQubits, size_t nCircuits,
+                                     const uint64_t* gateOffsets,
+                                     const int32_t* control,
+                                     const int32_t* target, int32_t layering,
+                                     qmg_circuit_batch** out) {
+  if (out == nullptr || (nCircuits > 0 && gateOffsets == nullptr)) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  try {
+    auto b = std::make_unique<qmg_circuit_batch>();
+    b->circ.resize(nCircuits);
+    std::atomic<int> bad{0};
+    std::string msg;
+    std::mutex mu;
+    qmg::parallelFor(nCircuits, 16, [&](size_t i) {
+      try {
+        const uint64_t lo = gateOffsets[i], hi = gateOffsets[i + 1];
+        b->circ[i].build(nArchQubits, static_cast<size_t>(hi - lo),
+                         control + lo, target + lo, layering);
+      } catch (const std::exception& e) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (bad.exchange(1) == 0) {
+          msg = e.what();
+        }
+      }
+    });
+    if (bad.load() != 0) {
+      return qmg::fail(QMG_BAD_ARG, msg);
+    }
+    *out = b.release();
+    return QMG_OK;
+  } catch (const std::exception& e) {
+    return qmg::fail(QMG_BAD_ARG, e.what());
+  }
+}
+namespace qmg {
+inline void layersOf(const FlatLayers& f, qmg_layers* out) {
+  out->n_layers = f.nLayers;
+  out->n_logical = f.nLogical;
+  out->gate2q_offsets = f.g2Off.data();
+  out->gates2q = reinterpret_cast<const qmg_gate2q*>(f.g2.data());
+  out->gate1q_offsets = f.g1Off.data();
+  out->gates1q = reinterpret_cast<const qmg_gate1q*>(f.g1.data());
+}
+}  // namespace qmg
+QMG_API int qmg_circuit_batch_layers(const qmg_circuit_batch* b, size_t i,
+                                     qmg_layers* out) {
+  if (b == nullptr || out == nullptr || i >= b->circ.size()) {
+    return qmg::fail(QMG_BAD_ARG, "circuit index out of range");
+  }
+  qmg::layersOf(b->circ[i], out);
+  return QMG_OK;
+}
+QMG_API int qmg_circuit_batch_fill_instances(const qmg_circuit_batch* b,
+                                             qmg_instance* instances,
+                                             size_t nInstances) {
+  if (b == nullptr || instances == nullptr || nInstances > b->circ.size()) {
+    return qmg::fail(QMG_BAD_ARG, "more instances than circuits");
+  }
+  for (size_t i = 0; i < nInstances; ++i) {
+    qmg::layersOf(b->circ[i], &instances[i].layers);
+  }
+  return QMG_OK;
+}
+QMG_API int qmg_circuit_batch_layer_gates(const qmg_circuit_batch* b, size_t i,
+                                          uint32_t* offsets,
+                                          uint32_t* gateIndices) {
+  if (b == nullptr || i >= b->circ.size()) {
+    return qmg::fail(QMG_BAD_ARG, "circuit index out of range");
+  }
+  const auto& f = b->circ[i];
+  std::memcpy(offsets, f.gateOff.data(), f.gateOff.size() * 4);
+  std::memcpy(gateIndices, f.gateIdx.data(), f.gateIdx.size() * 4);
+  return QMG_OK;
+}
+QMG_API void qmg_circuit_batch_destroy(qmg_circuit_batch* b) { delete b; }
+
+// Replay of routed instances (the output must be the input circuit
+// under the SWAP-induced permutation): starting from start_locations, every
+// layer's SWAPs must sit on coupling edges, after them every 2q gate of the
+// layer must act on adjacent physical qubits, qubits placed on the way follow
+// the placement list, and the layout reached must be final_locations.
+// verdict[i]: 1 = valid, 0 = invalid, 2 = not checkable (layers were split by
+// the library, outputs missing, or the instance did not finish).
+QMG_API int qmg_circuit_batch_verify(const qmg_circuit_batch* b, uint16_t n,
+                                     const uint16_t* edges, size_t nEdges,
+                                     const uint64_t* gateOffsets,
+                                     const int32_t* control,
+                                     const int32_t* target,
+                                     const qmg_route_result* results,
+                                     size_t nInstances,
+                                     int32_t fidelityAware, uint8_t* verdict) {
+  if (b == nullptr || results == nullptr || verdict == nullptr ||
+      nInstances > b->circ.size() || (nEdges > 0 && edges == nullptr)) {
+    return qmg::fail(QMG_BAD_ARG, "bad argument");
+  }
+  std::vector<uint8_t> adj(static_cast<size_t>(n) * n, 0);
+  for (size_t e = 0; e < nEdges; ++e) {
+    const uint16_t x = edges[2 * e], y = edges[2 * e + 1];
+    if (x >= n || y >= n) {
+      return qmg::fail(QMG_BAD_ARG, "coupling-map entry out of range");
+    }
+    adj[static_cast<size_t>(x) * n + y] = 1;
+    adj[static_cast<size_t>(y) * n + x] = 1;
+  }
+  qmg::parallelFor(nInstances, 64, [&](size_t i) {
+    const qmg::FlatLayers& f = b->circ[i];
+    const qmg_route_result& r = results[i];
+    verdict[i] = 2;
+    if (r.status != QMG_OK || r.n_splits != 0 || r.n_layers_done != f.nLayers ||
+        r.swaps == nullptr || r.start_locations == nullptr ||
+        r.final_locations == nullptr ||
+        (r.layer_n_swaps == nullptr && r.layers == nullptr) ||
+        r.n_swaps_total > r.swap_capacity) {
+      return;
+    }
+    std::vector<int32_t> loc(r.start_locations, r.start_locations + n);
+    std::vector<int32_t> at(n, -1);
+    bool ok = true;
+    for (int q = 0; q < n; ++q) {
+      if (loc[q] >= 0) {
+        ok = ok && loc[q] < n && at[loc[q]] == -1;
+        if (ok) {
+          at[loc[q]] = q;
+        }
+      }
+    }
+    const int32_t* ctrl = control + gateOffsets[i];
+    const int32_t* tgt = target + gateOffsets[i];
+    uint32_t sw = 0, pl = 0;
+    auto place = [&](int32_t q) {
+      // mapUnmappedGates placed q before this layer's search
+      while (ok && loc[q] < 0) {
+        if (r.placements == nullptr || pl >= r.n_placements_total ||
+            pl >= r.placement_capacity) {
+          ok = false;
+          break;
+        }
+        const qmg_placement p = r.placements[pl++];
+        ok = p.logical < n && p.physical < n && loc[p.logical] < 0 &&
+             at[p.physical] == -1;
+        if (ok) {
+          loc[p.logical] = p.physical;
+          at[p.physical] = p.logical;
+        }
+      }
+    };
+    for (uint32_t l = 0; l < f.nLayers && ok; ++l) {
+      // mapUnmappedGates :211-285: the fidelity-aware mapper places the
+      // qubits of the layer's 1q gates first (ascending), then the 2q gates'
+      if (fidelityAware != 0) {
+        for (uint32_t k = f.g1Off[l]; k < f.g1Off[l + 1] && ok; ++k) {
+          place(f.g1[k].q);
+        }
+      }
+      for (uint32_t k = f.g2Off[l]; k < f.g2Off[l + 1] && ok; ++k) {
+        const qmg::Gate2 e = f.g2[k];
+        // (which of the two is placed first depends on the other's state;
+        // either way both are placed before the layer's SWAPs)
+        if (loc[e.q1] < 0 || loc[e.q2] < 0) {
+          place(loc[e.q1] < 0 && loc[e.q2] >= 0 ? e.q1 : (loc[e.q2] < 0 && loc[e.q1] >= 0 ? e.q2 : e.q1));
+          place(e.q2);
+          place(e.q1);
+        }
+      }
+      const uint32_t ns = r.layer_n_swaps != nullptr ? r.layer_n_swaps[l]
+                                                     : r.layers[l].n_swaps;
+      for (uint32_t s = 0; s < ns && ok; ++s, ++sw) {
+        if (sw >= r.n_swaps_total) {
+          ok = false;
+          break;
+        }
+        const uint16_t x = r.swaps[2 * sw], y = r.swaps[2 * sw + 1];
+        ok = x < n && y < n && adj[static_cast<size_t>(x) * n + y] != 0;
+        if (ok) {
+          const int32_t qx = at[x], qy = at[y];
+          at[x] = qy;
+          at[y] = qx;
+          if (qx >= 0) {
+            loc[qx] = y;
+          }
+          if (qy >= 0) {
+            loc[qy] = x;
+          }
+        }
+      }
+      for (uint32_t k = f.gateOff[l]; k < f.gateOff[l + 1] && ok; ++k) {
+        const uint32_t gi = f.gateIdx[k];
+        if (ctrl[gi] >= 0) {
+          const int32_t pc = loc[ctrl[gi]], pt = loc[tgt[gi]];
+          ok = pc >= 0 && pt >= 0 && adj[static_cast<size_t>(pc) * n + pt] != 0;
+        }
+      }
+    }
+    ok = ok && sw == r.n_swaps_total;
+    for (int q = 0; q < n && ok; ++q) {
+      // (1q-only qubits of the fidelity-aware mapper are placed too; a qubit
+      // the replay never needed may still be unplaced here)
+      ok = loc[q] < 0 || loc[q] == r.final_locations[q];
+    }
+    verdict[i] = ok ? 1 : 0;
+  });
+  return QMG_OK;
+}
 #endif

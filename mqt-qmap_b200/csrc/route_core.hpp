@@ -178,7 +178,10 @@ struct InstView {
   // [4]=offset of the instance's SWAPs in swapsPacked [5]=layer splits of the
   // final pass
   uint32_t* summary;
-  uint64_t* counters;  // [0]=expanded [1]=generated (all passes)
+  // [0]=expanded [1]=generated (all passes) [2], [3] = the same for the final
+  // routing pass only (what the reference's heuristicBenchmark counts: it
+  // switches the counters off inside pseudoRouteCircuit, :309-344)
+  uint64_t* counters;
 };
 
 // entries of one layout array in a node record: n rounded up to a multiple of
@@ -814,6 +817,7 @@ template <int H, bool kFull> struct Search {
   bool maskReady = false;
   bool allowSplit = false;  // this aStarMap call may stop at the split limit
   uint64_t totExpanded = 0, totGenerated = 0;
+  uint64_t pseudoExpanded = 0, pseudoGenerated = 0;  // of the pseudo passes
 
   QMG_HD Search(const ArchView& a, const CfgView& c, InstView& i,
                 SearchMem& m, Scratch& s)
@@ -1695,12 +1699,41 @@ template <int H, bool kFull> struct Search {
                         bool root) {
     int16_t* q = nodeQ(idx);
     int16_t* l = nodeL(idx);
-    QMG_NOUNROLL
-    for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
-      st64(q + i0, ld64(pQ + i0));
-      st64(l + i0, ld64(pL + i0));
+    if (!kFull) {
+      // (short searches on small architectures: one entry per lane is fewer
+      // instructions than the word copy + patch; records of the lean variant
+      // are never compared word by word)
+      const int a = ch.a;
+      const int b = ch.b;
+      const int q1 = root ? -2 : pQ[a];
+      const int q2 = root ? -2 : pQ[b];
+      QMG_NOUNROLL
+      for (int i = g.lane; i < n; i += Group::W) {
+        int16_t vq = pQ[i];
+        int16_t vl = pL[i];
+        if (!root) {
+          if (i == a) {
+            vq = static_cast<int16_t>(q2);
+          } else if (i == b) {
+            vq = static_cast<int16_t>(q1);
+          }
+          if (i == q1) {
+            vl = static_cast<int16_t>(b);
+          } else if (i == q2) {
+            vl = static_cast<int16_t>(a);
+          }
+        }
+        q[i] = vq;
+        l[i] = vl;
+      }
+    } else {
+      QMG_NOUNROLL
+      for (int i0 = 4 * g.lane; i0 < n; i0 += 4 * Group::W) {
+        st64(q + i0, ld64(pQ + i0));
+        st64(l + i0, ld64(pL + i0));
+      }
     }
-    if (!root) {
+    if (kFull && !root) {
       g.sync();  // (orders the word stores before the entry stores)
       const int a = ch.a;
       const int b = ch.b;
@@ -1757,6 +1790,25 @@ template <int H, bool kFull> struct Search {
   // except at the entries a and b, where it must be pQ[a] XOR pQ[b].
   QMG_HD bool layoutDiffers(uint32_t idx, int a, int b) const {
     const int16_t* q = nodeQ(idx);
+    if (!kFull) {
+      bool df = false;
+      QMG_NOUNROLL
+      for (int i0 = 0; i0 < n; i0 += Group::W) {
+        const int i = i0 + g.lane;
+        if (i < n) {
+          int16_t v = pQ[i];
+          if (a >= 0) {
+            if (i == a) {
+              v = pQ[b];
+            } else if (i == b) {
+              v = pQ[a];
+            }
+          }
+          df = df || (q[i] != v);
+        }
+      }
+      return df;
+    }
     uint32_t d = 0;
     if (a >= 0) {
       d = (static_cast<uint32_t>(static_cast<uint16_t>(pQ[a])) ^
@@ -2886,6 +2938,8 @@ template <int H, bool kFull> struct Search {
       }
       const uint32_t first = I.firstLayer;
       doneLayers = first;
+      pseudoExpanded = totExpanded;
+      pseudoGenerated = totGenerated;
       QMG_NOUNROLL
       for (uint32_t l = first;; ++l) {
         const uint32_t nL = I.circ.nLayers;
@@ -2938,6 +2992,8 @@ template <int H, bool kFull> struct Search {
       I.summary[3] = static_cast<uint32_t>(rc);
       I.counters[0] = totExpanded;
       I.counters[1] = totGenerated;
+      I.counters[2] = totExpanded - pseudoExpanded;
+      I.counters[3] = totGenerated - pseudoGenerated;
     }
     g.sync();
     return true;

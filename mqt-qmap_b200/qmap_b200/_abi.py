@@ -87,6 +87,7 @@ class QmgRouteResult(C.Structure):
         ("layer_n_swaps", C.c_void_p),
         ("split_layers", C.c_void_p), ("split_capacity", C.c_uint32),
         ("n_splits", C.c_uint32),
+        ("expanded_nodes_final_pass", C.c_uint64), ("generated_nodes_final_pass", C.c_uint64),
     ]
 
 
@@ -137,6 +138,9 @@ EXPORTS = [
     "qmg_circuit_split_layer", "qmg_circuit_destroy", "qmg_route_batch",
     "qmg_batch_create", "qmg_batch_run", "qmg_batch_fetch", "qmg_batch_destroy",
     "qmg_last_error", "qmg_device_count", "qmg_version", "qmg_build_table_static",
+    "qmg_circuit_batch_create", "qmg_circuit_batch_layers", "qmg_circuit_batch_destroy",
+    "qmg_circuit_batch_fill_instances", "qmg_circuit_batch_layer_gates",
+    "qmg_circuit_batch_verify",
 ]
 
 _lib = None
@@ -154,6 +158,16 @@ def bind_host_api(L):
     L.qmg_circuit_split_layer.argtypes = [C.c_void_p, C.c_uint32]
     L.qmg_circuit_destroy.argtypes = [C.c_void_p]
     L.qmg_circuit_destroy.restype = None
+    L.qmg_circuit_batch_create.argtypes = [C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_int32, C.POINTER(C.c_void_p)]
+    L.qmg_circuit_batch_layers.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(QmgLayers)]
+    L.qmg_circuit_batch_fill_instances.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    L.qmg_circuit_batch_layer_gates.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.qmg_circuit_batch_verify.argtypes = [C.c_void_p, C.c_uint16, C.c_void_p, C.c_size_t, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int32,
+                                           C.c_void_p]
+    L.qmg_circuit_batch_destroy.argtypes = [C.c_void_p]
+    L.qmg_circuit_batch_destroy.restype = None
 
 
 def load(path: str = LIB_PATH):

@@ -37,8 +37,10 @@ class MappingResults:
     output_single_qubit_gates: int = 0
     layer_splits: int = 0
     rerouted_with_host_splits: bool = False
-    expanded_nodes: int = 0
+    expanded_nodes: int = 0  # final routing pass (heuristicBenchmark.expandedNodes)
     generated_nodes: int = 0
+    expanded_nodes_all_passes: int = 0  # incl. pseudo-routing passes
+    generated_nodes_all_passes: int = 0
     time: float = 0.0
     layer_n_swaps: np.ndarray | None = None
     config: object = None
@@ -167,8 +169,12 @@ class HeuristicMapper:
             if start_locations is None:
                 start_locations = out.start_locations.copy()
             done = out.n_layers_done
-            res.expanded_nodes += out.expanded_nodes
-            res.generated_nodes += out.generated_nodes
+            # heuristicBenchmark counts the final routing pass only (the
+            # reference switches its counters off in pseudoRouteCircuit)
+            res.expanded_nodes += out.expanded_nodes_final_pass
+            res.generated_nodes += out.generated_nodes_final_pass
+            res.expanded_nodes_all_passes += out.expanded_nodes
+            res.generated_nodes_all_passes += out.generated_nodes
             lq_parts.append(out.layer_qubits[first:done].copy())
             ns_parts.append(out.layer_n_swaps[first:done].copy())
             nsw = int(out.layer_n_swaps[first:done].sum())

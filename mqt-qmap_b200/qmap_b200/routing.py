@@ -135,6 +135,84 @@ class LayeredCircuit:
         self.splits.append(int(layer))
 
 
+class CircuitBatch:
+    """qmg_circuit_batch: Mapper::createLayers for many gate lists at once (host
+    threads, CSR layers only).  batch[i] is a light view usable as
+    RouteItem.circuit."""
+
+    class View:
+        def __init__(self, batch, i):
+            self.batch, self.i = batch, i
+
+        @property
+        def layers(self) -> QmgLayers:
+            v = QmgLayers()
+            _abi.check(self.batch.lib, self.batch.lib.qmg_circuit_batch_layers(
+                self.batch.h, self.i, C.byref(v)))
+            return v
+
+        @property
+        def n_layers(self) -> int:
+            return int(self.layers.n_layers)
+
+        def layer_gates(self):
+            lo, hi = self.batch.offsets[self.i], self.batch.offsets[self.i + 1]
+            off = np.zeros(self.n_layers + 1, dtype=np.uint32)
+            idx = np.zeros(int(hi - lo), dtype=np.uint32)
+            _abi.check(self.batch.lib, self.batch.lib.qmg_circuit_batch_layer_gates(
+                self.batch.h, self.i, off.ctypes.data, idx.ctypes.data))
+            return off, idx
+
+    def __init__(self, lib, n_arch_qubits: int, offsets, control, target, layering=0):
+        self.lib = lib
+        self.n = int(n_arch_qubits)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self.control = np.ascontiguousarray(control, dtype=np.int32)
+        self.target = np.ascontiguousarray(target, dtype=np.int32)
+        h = C.c_void_p()
+        _abi.check(lib, lib.qmg_circuit_batch_create(
+            self.n, len(self.offsets) - 1, self.offsets.ctypes.data, self.control.ctypes.data,
+            self.target.ctypes.data, int(layering), C.byref(h)))
+        self.h = h
+
+    @classmethod
+    def from_gate_lists(cls, lib, n_arch_qubits, gate_lists, layering=0):
+        """gate_lists: [(control, target)] arrays per circuit"""
+        sizes = [len(c) for c, _ in gate_lists]
+        off = np.concatenate(([0], np.cumsum(sizes))).astype(np.uint64)
+        ctrl = np.concatenate([np.asarray(c, dtype=np.int32) for c, _ in gate_lists]) \
+            if gate_lists else np.zeros(0, np.int32)
+        tgt = np.concatenate([np.asarray(t, dtype=np.int32) for _, t in gate_lists]) \
+            if gate_lists else np.zeros(0, np.int32)
+        return cls(lib, n_arch_qubits, off, ctrl, tgt, layering)
+
+    def __len__(self):
+        return len(self.offsets) - 1
+
+    def __getitem__(self, i):
+        return CircuitBatch.View(self, int(i))
+
+    def fill_instances(self, inst_array, n):
+        _abi.check(self.lib, self.lib.qmg_circuit_batch_fill_instances(
+            self.h, C.addressof(inst_array), n))
+
+    def verify(self, edges, res_array, n_instances, fidelity_aware=False) -> np.ndarray:
+        """qmg_circuit_batch_verify: replay of the routed instances; returns the
+        verdicts (1 valid, 0 invalid, 2 not checkable)."""
+        e = np.ascontiguousarray(edges, dtype=np.uint16).reshape(-1, 2)
+        v = np.zeros(n_instances, dtype=np.uint8)
+        _abi.check(self.lib, self.lib.qmg_circuit_batch_verify(
+            self.h, self.n, e.ctypes.data, len(e), self.offsets.ctypes.data,
+            self.control.ctypes.data, self.target.ctypes.data, C.addressof(res_array),
+            n_instances, int(bool(fidelity_aware)), v.ctypes.data))
+        return v
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.qmg_circuit_batch_destroy(self.h)
+            self.h = None
+
+
 @dataclass
 class RouteItem:
     circuit: LayeredCircuit
@@ -159,6 +237,8 @@ class RouteOutput:
     layer_qubits: np.ndarray | None = None
     layer_n_swaps: np.ndarray | None = None  # uint16 per layer
     split_layers: np.ndarray | None = None  # layers split by the backend (final pass)
+    expanded_nodes_final_pass: int = 0  # the reference's heuristicBenchmark counters
+    generated_nodes_final_pass: int = 0
     _offsets: np.ndarray | None = None
 
     def layer_swaps(self, layer: int) -> np.ndarray:
@@ -267,6 +347,8 @@ def unpack(b: BatchBuffers) -> list:
             placements=b.places[i][: int(r.n_placements_total)],
             final_qubits=b.fq[i], final_locations=b.fl[i], start_locations=b.sl[i],
             layer_qubits=b.lq[i][:nl] if b.lq else None,
+            expanded_nodes_final_pass=int(r.expanded_nodes_final_pass),
+            generated_nodes_final_pass=int(r.generated_nodes_final_pass),
             split_layers=(b.split_logs[i][: min(int(r.n_splits), len(b.split_logs[i]))]
                           if b.split_logs else None)))
     return outs

@@ -68,6 +68,29 @@ def c3_instance(circuit_dir: str, seed: int, n_physical: int = 27):
     return f, wide.relabel(rng.permutation(n_physical))
 
 
+def c3_passes(circuit_dir: str, seed: int) -> int:
+    """Bidirectional pseudo-routing passes of instance `seed`: every placement
+    of the suite is routed forward only (even rounds over the suite) and with
+    one bidirectional pass (odd rounds), BASELINE.md section 3.3."""
+    return (seed // len(c3_suite(circuit_dir))) % 2
+
+
+def c3_instance_passes(circuit_dir: str, seed: int, n_physical: int = 27):
+    f, circ = c3_instance(circuit_dir, seed, n_physical)
+    return f, circ, c3_passes(circuit_dir, seed)
+
+
+def c3_directory(root: str) -> str:
+    """The circuit suite of config 3: all of the reference's examples/*.qasm
+    where tools/fetch_examples.py has copied them (tests/golden/circuits_full,
+    git-ignored, travels to the GPU box), else the committed 22-circuit subset
+    (tests/golden/circuits)."""
+    full = os.path.join(root, "tests", "golden", "circuits_full")
+    if os.path.isdir(full) and any(f.endswith(".qasm") for f in os.listdir(full)):
+        return full
+    return os.path.join(root, "tests", "golden", "circuits")
+
+
 def c3_instances(circuit_dir: str, copies: int, first_seed: int = 0, n_physical: int = 27):
     """[(file name, Circuit)] for seeds first_seed .. first_seed + copies * |suite|."""
     k = len(c3_suite(circuit_dir))

@@ -248,7 +248,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     I.layerQ = r.layer_qubits;
     uint32_t summary[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     I.layerNSwaps = r.layer_n_swaps;
-    uint64_t counters[2] = {0, 0};
+    uint64_t counters[4] = {0, 0, 0, 0};
     I.summary = summary;
     I.counters = counters;
     switch (C.heuristic) {
@@ -266,6 +266,8 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     r.status = static_cast<int32_t>(summary[3]);
     r.expanded_nodes = counters[0];
     r.generated_nodes = counters[1];
+    r.expanded_nodes_final_pass = counters[2];
+    r.generated_nodes_final_pass = counters[3];
   }
   return QMG_OK;
 }

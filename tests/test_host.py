@@ -207,3 +207,54 @@ def test_instance_sharding_world_size_2(tmp_path):
          "--master-addr", "127.0.0.1", "--master-port", "29631", str(script)],
         capture_output=True, text=True, env=env, timeout=600)
     assert "SHARDS_OK" in out.stdout, out.stdout + out.stderr
+
+
+def _layers_arrays(lay):
+    nl = int(lay.n_layers)
+    o2 = np.ctypeslib.as_array(C.cast(lay.gate2q_offsets, C.POINTER(C.c_uint32)), (nl + 1,)).copy()
+    o1 = np.ctypeslib.as_array(C.cast(lay.gate1q_offsets, C.POINTER(C.c_uint32)), (nl + 1,)).copy()
+    g2 = (np.ctypeslib.as_array(C.cast(lay.gates2q, C.POINTER(C.c_uint16)), (int(o2[-1]) * 4,)).copy()
+          if o2[-1] else np.zeros(0, np.uint16))
+    g1 = (np.ctypeslib.as_array(C.cast(lay.gates1q, C.POINTER(C.c_uint16)), (int(o1[-1]) * 2,)).copy()
+          if o1[-1] else np.zeros(0, np.uint16))
+    return nl, int(lay.n_logical), o2, o1, g2, g1
+
+
+@pytest.mark.parametrize("layering", [0, 1, 4])
+def test_circuit_batch_layers_equal_layered_circuit(layering):
+    """qmg_circuit_batch_create (CSR-only createLayers, host threads) against
+    qmg_circuit_create (the per-layer containers of the reference), array by
+    array, on random circuits and the golden suite."""
+    L = _abi.load()
+    rng = np.random.default_rng(layering)
+    lists = []
+    for k in range(60):
+        n = int(rng.integers(2, 12))
+        m = int(rng.integers(0, 80))
+        c = np.full(m, -1, dtype=np.int32)
+        t = rng.integers(0, n, m).astype(np.int32)
+        two = rng.random(m) < 0.6
+        for i in np.nonzero(two)[0]:
+            c[i] = (t[i] + 1 + rng.integers(0, n - 1)) % n
+        lists.append((c, t))
+    suite = os.path.join(ROOT, "tests", "golden", "circuits")
+    for f in sorted(os.listdir(suite))[:8]:
+        lists.append(qcirc.load_qasm(os.path.join(suite, f)).gate_arrays())
+    batch = routing.CircuitBatch.from_gate_lists(L, 16, lists, layering)
+    assert len(batch) == len(lists)
+    for i, (c, t) in enumerate(lists):
+        one = routing.LayeredCircuit(L, 16, c, t, layering)
+        a, b = _layers_arrays(batch[i].layers), _layers_arrays(one.layers)
+        assert a[0] == b[0] and a[1] == b[1], i
+        for x, y in zip(a[2:], b[2:]):
+            assert np.array_equal(x, y), i
+        for x, y in zip(batch[i].layer_gates(), one.layer_gates()):
+            assert np.array_equal(x, y), i
+
+
+def test_circuit_batch_rejects_bad_operands():
+    L = _abi.load()
+    with pytest.raises(_abi.QmapError):
+        routing.CircuitBatch.from_gate_lists(L, 4, [(np.array([0]), np.array([4]))], 0)
+    with pytest.raises(_abi.QmapError):
+        routing.CircuitBatch.from_gate_lists(L, 4, [(np.array([0]), np.array([1]))], 2)

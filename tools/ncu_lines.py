@@ -37,7 +37,8 @@ for r in data:
     for k, i in ist.items(): stl[key][k] += int(r[i] or 0)
 tot = sum(agg.values()); stot = sum(sagg.values())
 print("total inst", tot, "static", len(data), "samples", stot)
-src = open(os.path.join(os.path.dirname(os.path.abspath(lib)), "route_core.hpp")).read().split("\n") if os.path.exists(os.path.join(os.path.dirname(os.path.abspath(lib)), "route_core.hpp")) else open("/root/repo/mqt-qmap_b200/csrc/route_core.hpp").read().split("\n")
+# the source the capture was built from (NCU_SRC=path; default: the tree's)
+src = open(os.environ.get("NCU_SRC", "/root/repo/mqt-qmap_b200/csrc/route_core.hpp")).read().split("\n")
 for k, n in sagg.most_common(top):
     txt = src[k[1] - 1].strip()[:60] if k and k[0] == "route_core.hpp" else ""
     print(k, "samp%", round(100 * n / stot, 1), "inst%", round(100 * agg[k] / tot, 1), "static", static[k], dict(stl[k].most_common(2)), "|", txt)
