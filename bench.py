@@ -565,6 +565,9 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu):
     bad = [o.status for o in outs if o.status != 0]
     if bad:
         raise RuntimeError(f"{len(bad)} instances failed, first status {bad[0]}")
+    ex = np.sort(np.array([o.expanded_nodes for o in outs]))[::-1]
+    log(f"{wl.key}: expanded nodes per instance: max {ex[:5].tolist()}, mean {ex.mean():.0f}, "
+        f"median {int(np.median(ex))}, sum {int(ex.sum())}; per resident search {ex.sum() / (stats.grid * 4):.0f}")
     exp = sum(o.expanded_nodes for o in outs)
     gen = sum(o.generated_nodes for o in outs)
     swaps = sum(len(o.swaps) for o in outs)
@@ -675,6 +678,8 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu):
                 "scope": "route only: qmg_route_batch on host buffers (layers built before); staging, H2D, "
                          "kernel, D2H of SWAP lists + layouts inside the timed region",
                 "kernel_launches_per_call": int(st2.kernel_launches),
+                "layers_in_large_pools": int(st2.big_pool_layers),
+                "retried_instances": int(st2.retried_instances),
                 "last_call_ms": {"stage_h2d": float(st2.h2d_ms), "kernel": float(st2.kernel_ms),
                                  "d2h_scatter": float(st2.d2h_ms)}},
         "e2e_full": {"value": exp_all * len(full_ms) / t_full, "unit": "nodes/s",

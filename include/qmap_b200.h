@@ -431,6 +431,16 @@ typedef struct {
    * variant from the start (long searches expected), 2 = lean first,
    * 0 = auto (full for fidelity-aware routing on more than 32 qubits). */
   uint32_t search_variant;
+  /* Node pools come in two tiers: a private pool per resident search
+   * (pool_nodes; auto = a share of the memory budget) and a few large pools
+   * shared by the whole launch, which a search takes for a layer that outgrows
+   * its private pool (the search state moves to the large pool and the
+   * search carries on there; results are unchanged).  big_pools: number of large pools, 0 = auto (32 with
+   * automatic pool sizes, none with an explicit pool_nodes), 0xFFFFFFFF = none.
+   * big_pool_nodes: their capacity in nodes (needed with an explicit
+   * pool_nodes, else auto). */
+  uint32_t big_pools;
+  uint32_t big_pool_nodes;
 } qmg_route_options;
 
 typedef struct {
@@ -449,6 +459,8 @@ typedef struct {
    * (up to three such rounds; an instance still failing keeps
    * QMG_POOL_EXHAUSTED) */
   uint32_t retried_instances;
+  /* layers that were searched in one of the launch's large pools */
+  uint32_t big_pool_layers;
 } qmg_route_stats;
 
 /*

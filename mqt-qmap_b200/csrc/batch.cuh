@@ -35,7 +35,8 @@ struct qmg_batch {
   // input arena offsets of what the launch needs
   size_t iInst = 0, iOrder = 0, iMem = 0, iTicket = 0, inSize = 0;
   size_t tableOff = 0, tableBytes = 0;
-  uint32_t grid = 0, poolNodes = 0;
+  uint32_t grid = 0, poolNodes = 0, nBig = 0, bigNodes = 0;
+  size_t bigTableOff = 0, bigTableBytes = 0, iBig = 0;
   uint32_t startFull = 0;  // route_kernel: full search variant from the start
   Scratch sl{};
   size_t smemBytes = 0;
@@ -280,6 +281,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   const uint32_t nWarps = b->grid * kWarpsPerCta;
   const uint32_t recBytes = nodeRecBytes(n);
   uint32_t poolNodes = (opt != nullptr) ? opt->pool_nodes : 0U;
+  uint32_t nBig = 0, bigNodes = 0;
   if (poolNodes == 0) {
     if (W.memBudget == 0) {
       size_t freeB = 0, totalB = 0;
@@ -298,15 +300,54 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     }
     const size_t budget = W.memBudget;
     const size_t perNode = recBytes + sizeof(OpenEntry) + 4 * sizeof(uint64_t);
+    // Two tiers: every resident search owns a private pool sized for the
+    // common case (a share of the budget), the rest of the budget is a few
+    // large pools that searches take for the layers that outgrow the private
+    // one (BigPool, route_core.hpp).  QMAP_B200_BIG_POOLS / _PRIVATE_PCT tune
+    // the split (0 large pools = the whole budget in private pools).
+    nBig = (opt != nullptr && opt->big_pools != 0) ? opt->big_pools : 32U;
+    size_t privatePct = 40;
+    if (const char* e = std::getenv("QMAP_B200_BIG_POOLS")) {
+      nBig = static_cast<uint32_t>(std::max(0L, std::atol(e)));
+    }
+    if (const char* e = std::getenv("QMAP_B200_PRIVATE_PCT")) {
+      privatePct = static_cast<size_t>(std::min(100L, std::max(1L, std::atol(e))));
+    }
+    if (opt != nullptr && opt->big_pools == 0xFFFFFFFFU) {
+      nBig = 0;
+    }
+    nBig = std::min<uint32_t>(nBig, std::max<uint32_t>(1, nWarps / 8));
     size_t pn = budget / (static_cast<size_t>(nWarps) * perNode);
+    if (nBig > 0) {
+      const size_t pnShare =
+          std::max<size_t>(1024, std::min<size_t>(pn * privatePct / 100, W.poolCapNodes));
+      const size_t used = pnShare * nWarps * perNode;
+      const size_t bn = used < budget ? (budget - used) / (nBig * perNode) : 0;
+      if (bn >= 4 * pnShare) {
+        pn = pnShare;
+        bigNodes = static_cast<uint32_t>(std::min<size_t>(bn, kMaxPoolNodes));
+      } else {
+        nBig = 0;  // (a budget too small for two tiers)
+      }
+    }
     pn = std::min<size_t>(pn, W.poolCapNodes);
     pn = std::max<size_t>(pn, 1024);
     poolNodes = static_cast<uint32_t>(std::min<size_t>(pn, kMaxPoolNodes));
+  } else if (opt->big_pools != 0 && opt->big_pools != 0xFFFFFFFFU &&
+             opt->big_pool_nodes != 0) {
+    nBig = opt->big_pools;
+    bigNodes = std::min<uint32_t>(opt->big_pool_nodes, kMaxPoolNodes);
+  }
+  if (nBig == 0 || bigNodes == 0) {
+    nBig = 0;
+    bigNodes = 0;
   }
   if (poolNodes > kMaxPoolNodes) {
     return fail(QMG_BAD_ARG, "pool_nodes exceeds 2^26 - 1 nodes per search");
   }
   b->poolNodes = poolNodes;
+  b->nBig = nBig;
+  b->bigNodes = bigNodes;
   {
     const uint32_t v = opt != nullptr ? opt->search_variant : 0U;
     b->startFull = v == 1 || (v == 0 && cfg->heuristic >= 4 && n > 32) ? 1U : 0U;
@@ -330,6 +371,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->iInst = li.add(nInst * sizeof(InstView));
   b->iOrder = li.add(nInst * 4);
   b->iMem = li.add(static_cast<size_t>(nWarps) * sizeof(SearchMem));
+  b->iBig = li.add(static_cast<size_t>(nBig) * sizeof(BigPool));
   b->inSize = li.size;
   // device-only tail of the input arena: the tables derived on the device
   Layout ld;
@@ -376,6 +418,17 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       lw.add(static_cast<size_t>(nWarps) * btopPerWarp * sizeof(OpenEntry));
   b->tableOff = wTable;
   b->tableBytes = wPairEnd - wTable;
+  uint32_t bigTableSize = 1;
+  while (nBig > 0 && bigTableSize < 2 * bigNodes) {
+    bigTableSize <<= 1;
+  }
+  const size_t bigBtop = bigNodes / kBlk + 2;
+  const size_t wBigPool = lw.add(static_cast<size_t>(nBig) * bigNodes * recBytes);
+  const size_t wBigOpen = lw.add(static_cast<size_t>(nBig) * bigNodes * sizeof(OpenEntry));
+  const size_t wBigTable = lw.add(nBig > 0 ? static_cast<size_t>(nBig) * bigTableSize * 8 : 0);
+  const size_t wBigBtop = lw.add(static_cast<size_t>(nBig) * bigBtop * sizeof(OpenEntry));
+  b->bigTableOff = wBigTable;
+  b->bigTableBytes = nBig > 0 ? static_cast<size_t>(nBig) * bigTableSize * 8 : 0;
 
   if (!W.hin.ensure(b->inSize) || !W.hout.ensure(pinnedOut)) {
     return fail(QMG_OOM, "pinned host allocation failed");
@@ -603,6 +656,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       }
       M.nsw = at<uint16_t>(Wk, wNsw) + static_cast<size_t>(w) * 32 * maxG;
       M.poolCap = poolNodes;
+      M.bigHeld = -1;
+      M.big = nBig > 0 ? at<BigPool>(D, b->iBig) : nullptr;
+      M.nBig = nBig;
       M.recBytes = recBytes;
       M.tableMask = tableSize - 1;
       M.stamp = 0;
@@ -615,6 +671,16 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       }
     }
   }
+  for (uint32_t k = 0; k < nBig; ++k) {
+    BigPool& P = at<BigPool>(H, b->iBig)[k];
+    P = BigPool{};
+    P.pool = Wk + wBigPool + static_cast<size_t>(k) * bigNodes * recBytes;
+    P.open = at<OpenEntry>(Wk, wBigOpen) + static_cast<size_t>(k) * bigNodes;
+    P.table = at<uint64_t>(Wk, wBigTable) + static_cast<size_t>(k) * bigTableSize;
+    P.btop = at<OpenEntry>(Wk, wBigBtop) + static_cast<size_t>(k) * bigBtop;
+    P.poolCap = bigNodes;
+    P.tableMask = bigTableSize - 1;
+  }
   sc.mark("views");
   // (the circuit ranges are already on their way)
   CU(cudaMemcpyAsync(D + circBytes, H + circBytes, b->inSize - circBytes,
@@ -625,6 +691,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     CU(cudaGetLastError());
   }
   CU(cudaMemsetAsync(Wk + b->tableOff, 0, b->tableBytes, s));
+  if (b->bigTableBytes != 0) {
+    CU(cudaMemsetAsync(Wk + b->bigTableOff, 0, b->bigTableBytes, s));
+  }
   b->h2dBytes = b->inSize;
   {
     const int sb = static_cast<int>(b->smemBytes);
@@ -793,6 +862,7 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
                         std::chrono::steady_clock::now() - t0)
                         .count();
     stats->d2h_bytes = std::max(end2, b->oSmallEnd);
+    stats->big_pool_layers = at<uint32_t>(Hh, b->oSwapCounter)[2];
     stats->expanded_nodes = exp.load();
     stats->generated_nodes = gen.load();
   }
@@ -917,6 +987,7 @@ QMG_API int qmg_route_batch(const qmg_arch* arch, const qmg_config* cfg,
         stats->d2h_bytes += st2.d2h_bytes;
         stats->kernel_launches += st2.kernel_launches;
         stats->retried_instances += static_cast<uint32_t>(idx.size());
+        stats->big_pool_layers += st2.big_pool_layers;
       }
     }
     if (retried) {

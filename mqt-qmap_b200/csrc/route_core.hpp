@@ -256,6 +256,22 @@ struct Child {
   uint32_t pad;
 };
 
+// A large node pool shared by all searches of a launch.  Every resident
+// search owns a small private pool (SearchMem::pool ...); a search whose layer
+// outgrows it takes one of the few large pools for the rest of that layer
+// (Search::migrateToBig) and carries on there with its state.  The
+// private pools can then be sized for the common case instead of the worst
+// one, which is what lets more searches stay resident per SM.
+struct BigPool {
+  uint8_t* pool;
+  OpenEntry* open;
+  uint64_t* table;
+  OpenEntry* btop;
+  uint32_t poolCap, tableMask;
+  uint32_t lock;   // 0 free, 1 held (atomicCAS)
+  uint32_t stamp;  // table stamp of the last holder (24 bits used)
+};
+
 // per resident search, in global memory
 struct SearchMem {
   uint8_t* pool;
@@ -279,6 +295,18 @@ struct SearchMem {
   uint8_t* priv;
   uint32_t epoch;       // splits of the layer being searched so far
   uint32_t childExtra;  // NodeHdr::extra of the children being generated
+  // large pools of the launch (null / 0: none) and, while one is held, its
+  // index and the private pool's fields it replaced
+  BigPool* big;
+  uint32_t nBig;
+  int32_t bigHeld;     // -1: the search runs in its private pool
+  uint32_t tabStampV;  // stamp written into table entries by this call
+  uint32_t poolCap0, tableMask0;
+  uint8_t* pool0;
+  OpenEntry* open0;
+  uint64_t* table0;
+  OpenEntry* btop0;
+  uint64_t bigUses;    // (statistics) layers this search ran in a large pool
 };
 
 // per resident search, in shared memory (device) / one byte buffer (host).
@@ -1846,7 +1874,7 @@ template <int H, bool kFull> struct Search {
   QMG_HD uint32_t homeSlot(uint64_t h) const {
     return static_cast<uint32_t>(h ^ (h >> 32)) & M.tableMask;
   }
-  QMG_HD uint32_t curStamp() const { return M.stamp & kStampMask; }
+  QMG_HD uint32_t curStamp() const { return M.tabStampV & kStampMask; }
 
   // switch from scanning the open list to the layout-keyed hash table
   QMG_HD void buildTable() {
@@ -2439,6 +2467,150 @@ template <int H, bool kFull> struct Search {
     g.sync();
   }
 
+  // a fresh stamp for the entries this aStarMap call writes into the hash
+  // table it uses (24 bits; when they wrap the table is cleared).  The private
+  // table counts with the search's own M.stamp, a large pool's table with the
+  // pool's counter (its holders change).  Group-uniform.
+  QMG_HD void newTableStamp() {
+    const bool inBig = kFull && M.bigHeld >= 0;
+    uint32_t s = inBig ? M.big[M.bigHeld].stamp + 1U : M.stamp;
+    g.sync();
+    if ((s & kStampMask) == 0) {
+      QMG_NOUNROLL
+      for (uint32_t i = g.lane; i <= M.tableMask; i += Group::W) {
+        M.table[i] = 0;
+      }
+      ++s;
+    }
+    if (g.lane == 0) {
+      if (inBig) {
+        M.big[M.bigHeld].stamp = s;
+      } else {
+        M.stamp = s;
+      }
+      M.tabStampV = s;
+    }
+    g.sync();
+  }
+
+  // take one of the launch's large pools (waiting for one to come free) and
+  // run in it until releaseBig(); false: the launch has none
+  QMG_HD bool acquireBig() {
+    if (!kFull || M.big == nullptr || M.nBig == 0 || M.bigHeld >= 0) {
+      return false;
+    }
+    g.sync();
+    int32_t got = -1;
+    if (g.lane == 0) {
+      uint32_t i = static_cast<uint32_t>(M.stamp * 2654435761U) % M.nBig;
+      for (;;) {
+#if defined(__CUDA_ARCH__)
+        if (atomicCAS(&M.big[i].lock, 0U, 1U) == 0U) {
+          got = static_cast<int32_t>(i);
+          break;
+        }
+        i = (i + 1) % M.nBig;
+        if (i == 0) {
+          __nanosleep(2000);
+        }
+#else
+        if (M.big[i].lock == 0U) {
+          M.big[i].lock = 1U;
+          got = static_cast<int32_t>(i);
+          break;
+        }
+        i = (i + 1) % M.nBig;
+        if (i == 0) {
+          break;  // (single-threaded host build: nobody will release one)
+        }
+#endif
+      }
+#if defined(__CUDA_ARCH__)
+      __threadfence();
+#endif
+    }
+    got = g.bcast(got, 0);
+    if (got < 0) {
+      return false;
+    }
+    if (g.lane == 0) {
+      const BigPool b = M.big[got];
+      M.pool0 = M.pool;
+      M.open0 = M.open;
+      M.table0 = M.table;
+      M.btop0 = M.btop;
+      M.poolCap0 = M.poolCap;
+      M.tableMask0 = M.tableMask;
+      M.pool = b.pool;
+      M.open = b.open;
+      M.table = b.table;
+      M.btop = b.btop;
+      M.poolCap = b.poolCap;
+      M.tableMask = b.tableMask;
+      M.bigHeld = got;
+      ++M.bigUses;
+      if (I.swapCounter != nullptr) {
+        // ([2] of the batch-wide counters: layers searched in a large pool)
+#if defined(__CUDA_ARCH__)
+        atomicAdd(I.swapCounter + 2, 1U);
+#else
+        ++I.swapCounter[2];
+#endif
+      }
+    }
+    g.sync();
+    return true;
+  }
+  // The private pool is about to fill up: the search state moves to one of
+  // the launch's large pools - node records and open list keep their indices,
+  // the hash table and the block tops are rebuilt - and the search goes on
+  // there until the layer is done.  No-op without large pools.
+  QMG_HD void migrateToBig() {
+    if (!kFull || M.bigHeld >= 0 || !acquireBig()) {
+      return;
+    }
+    const uint64_t* src = reinterpret_cast<const uint64_t*>(M.pool0);
+    uint64_t* dst = reinterpret_cast<uint64_t*>(M.pool);
+    const size_t words = static_cast<size_t>(nPool) * M.recBytes / 8U;
+    QMG_NOUNROLL
+    for (size_t w = g.lane; w < words; w += Group::W) {
+      dst[w] = src[w];
+    }
+    QMG_NOUNROLL
+    for (uint32_t i = g.lane; i < nOpen; i += Group::W) {
+      M.open[i] = M.open0[i];
+    }
+    g.sync();
+    newTableStamp();
+    if (tableMode) {
+      buildTable();
+    }
+    if (blockMode) {
+      blkEnter(octx(), M.open, M.btop, nOpen);
+    }
+    g.sync();
+  }
+  QMG_HD void releaseBig() {
+    g.sync();
+    if (g.lane == 0) {
+      const int32_t i = M.bigHeld;
+      M.pool = M.pool0;
+      M.open = M.open0;
+      M.table = M.table0;
+      M.btop = M.btop0;
+      M.poolCap = M.poolCap0;
+      M.tableMask = M.tableMask0;
+      M.bigHeld = -1;
+#if defined(__CUDA_ARCH__)
+      __threadfence();
+      atomicExch(&M.big[i].lock, 0U);
+#else
+      M.big[i].lock = 0U;
+#endif
+    }
+    g.sync();
+  }
+
   // resume: the call restarts on a layer that was just split and inherits the
   // open list of the interrupted call (:575-583 - `nodes` is not cleared)
   QMG_HD int astar(LayerStats& st, bool resume) {
@@ -2457,17 +2629,8 @@ template <int H, bool kFull> struct Search {
       M.epoch = M.epoch + 1 < kMaxEpochs ? M.epoch + 1 : kMaxEpochs - 1;
     }
     g.sync();
-    if (!resume && (M.stamp & kStampMask) == 0) {
-      // the 24 stamp bits of the table entries wrapped: forget every entry
-      QMG_NOUNROLL
-      for (uint32_t i = g.lane; i <= M.tableMask; i += Group::W) {
-        M.table[i] = 0;
-      }
-      g.sync();
-      if (g.lane == 0) {
-        ++M.stamp;
-      }
-      g.sync();
+    if (!resume) {
+      newTableStamp();
     }
     if (kFull && g.lane == 0) {
       M.childExtra = 0;
@@ -2506,6 +2669,13 @@ template <int H, bool kFull> struct Search {
     const bool rootLookWanted = record && I.layers != nullptr;
     QMG_NOUNROLL
     for (;;) {
+      // room for a chunk of new nodes: a private pool that is about to fill
+      // up hands the search over to one of the launch's large pools (the
+      // state moves, nothing is repeated)
+      if (kFull && nPool + static_cast<uint32_t>(kChunk) > M.poolCap &&
+          M.bigHeld < 0 && M.big != nullptr) {
+        migrateToBig();
+      }
       const int cnt = rootMode ? 1 : gatherChunk();
       if (cnt > 0) {
         evaluate(cnt, rootMode, pc, parentHash);
@@ -2716,6 +2886,15 @@ template <int H, bool kFull> struct Search {
 
   QMG_HD int routeLayer(uint32_t l, bool finalPass, bool reverse,
                         uint32_t& swapTotal) {
+    const int rc = routeLayerIn(l, finalPass, reverse, swapTotal);
+    // (a large pool is held for one layer: its result has been adopted)
+    if (kFull && M.bigHeld >= 0) {
+      releaseBig();
+    }
+    return rc;
+  }
+  QMG_HD int routeLayerIn(uint32_t l, bool finalPass, bool reverse,
+                          uint32_t& swapTotal) {
     const bool wantRec = finalPass && I.layers != nullptr;
     if (!kFid && !wantRec) {
       // a layer without 2q gates needs no search when no record of it is
@@ -2758,6 +2937,13 @@ template <int H, bool kFull> struct Search {
       allowSplit = finalPass || devSplit;
       st = LayerStats{};
       rc = astar(st, resume);
+      if (rc == ST_POOL) {
+        // (the full variant moves to a large pool before its private pool
+        // fills up, see astar; the lean one hands the instance over)
+        if (!kFull) {
+          return ST_NEEDS_FULL;
+        }
+      }
       if (rc != ST_SPLIT || !devSplit) {
         break;
       }

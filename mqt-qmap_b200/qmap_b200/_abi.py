@@ -94,7 +94,8 @@ class QmgRouteResult(C.Structure):
 class QmgRouteOptions(C.Structure):
     _fields_ = [("pool_nodes", C.c_uint32), ("threads_per_search", C.c_uint32),
                 ("searches_per_sm", C.c_uint32), ("lean_outputs", C.c_uint32),
-                ("max_searches", C.c_uint32), ("search_variant", C.c_uint32)]
+                ("max_searches", C.c_uint32), ("search_variant", C.c_uint32),
+                ("big_pools", C.c_uint32), ("big_pool_nodes", C.c_uint32)]
 
 
 class QmgRouteStats(C.Structure):
@@ -104,6 +105,7 @@ class QmgRouteStats(C.Structure):
         ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
         ("expanded_nodes", C.c_uint64), ("generated_nodes", C.c_uint64),
         ("kernel_launches", C.c_uint32), ("retried_instances", C.c_uint32),
+        ("big_pool_layers", C.c_uint32),
     ]
 
 

@@ -138,7 +138,30 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     tableSize <<= 1;
   }
   const uint32_t recBytes = nodeRecBytes(n);
-  std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8);
+  // QMG_EMU_PRIVATE_POOL=N: a private pool of N nodes and one large pool of
+  // poolNodes nodes (the two tiers of the CUDA batches, BigPool)
+  BigPool bigPool{};
+  std::vector<uint64_t> bigStore, bigTable;
+  std::vector<OpenEntry> bigOpen, bigBtop;
+  if (const char* e = std::getenv("QMG_EMU_PRIVATE_POOL")) {
+    const uint32_t priv = static_cast<uint32_t>(std::max(1, std::atoi(e)));
+    bigStore.resize(static_cast<size_t>(poolNodes) * recBytes / 8);
+    bigOpen.resize(poolNodes);
+    bigTable.assign(tableSize, 0);
+    bigBtop.resize(poolNodes / kBlk + 2);
+    bigPool.pool = reinterpret_cast<uint8_t*>(bigStore.data());
+    bigPool.open = bigOpen.data();
+    bigPool.table = bigTable.data();
+    bigPool.btop = bigBtop.data();
+    bigPool.poolCap = poolNodes;
+    bigPool.tableMask = tableSize - 1;
+    poolNodes = priv;
+    tableSize = 1;
+    while (tableSize < 2 * poolNodes) {
+      tableSize <<= 1;
+    }
+  }
+  std::vector<uint64_t> poolStore(static_cast<size_t>(poolNodes) * recBytes / 8 + 1);
   std::vector<OpenEntry> open(poolNodes);
   std::vector<uint64_t> table(tableSize, 0);
   Scratch S = scratchLayout(n);
@@ -214,6 +237,9 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     }
     M.nsw = nsw.data();
     M.poolCap = poolNodes;
+    M.bigHeld = -1;
+    M.big = bigPool.poolCap != 0 ? &bigPool : nullptr;
+    M.nBig = bigPool.poolCap != 0 ? 1U : 0U;
     M.recBytes = recBytes;
     M.tableMask = tableSize - 1;
     M.stamp = stamp;

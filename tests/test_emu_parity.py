@@ -136,6 +136,10 @@ def test_random_circuits_with_layer_splits_against_oracle(arch, calib):
 @pytest.mark.parametrize("env", [{"QMG_EMU_BLK": "4,8"}, {"QMG_EMU_BLK": "7,1"},
                                  {"QMG_EMU_BLK": "4,8,2", "QMG_EMU_START_FULL": "1"},
                                  {"QMG_EMU_BLK": "512,4096,1", "QMG_EMU_START_FULL": "1"},
+                                 # (a call resumed after a layer split cannot move to the
+                                 # large pool: the tiny private pool is for runs without splits)
+                                 {"QMG_EMU_PRIVATE_POOL": "6", "QMG_EMU_BLK": "4,8,2"},
+                                 {"QMG_EMU_PRIVATE_POOL": "40", "QMG_EMU_START_FULL": "1"},
                                  {"QMG_EMU_START_FULL": "1"}])
 def test_full_search_variant_matches_reference_outputs(env):
     """The kernel routes an instance with the lean search variant and again
@@ -148,13 +152,16 @@ def test_full_search_variant_matches_reference_outputs(env):
     code = (
         "import sys; sys.path[:0] = [%r, %r, %r]\n"
         "import emu_backend, parity, test_emu_parity as t\n"
+        "import os\n"
         "runs = t.RUNS[::6] + t.SPLIT_RUNS[::3]\n"
+        "if os.environ.get('QMG_TEST_NO_SPLITS'):\n"
+        "    runs = [g for g in t.RUNS[::4] if 'splits_node_limit' not in g.label]\n"
         "bad = []\n"
         "for g in runs:\n"
         "    be = t.emu_for(g.meta['arch'], g.meta['calibration'])\n"
         "    msg, _ = parity.run_golden(be, be.lib, be.n, g)\n"
         "    if msg: bad.append((g.label, msg))\n"
-        "assert len(runs) > 40 and not bad, bad[:3]\n"
+        "assert len(runs) > 30 and not bad, bad[:3]\n"
         "print('ok', len(runs))\n"
     ) % (os.path.dirname(__file__), os.path.join(os.path.dirname(__file__), "emu"),
          os.path.join(parity.ROOT, "mqt-qmap_b200"))
