@@ -74,7 +74,7 @@ def test_option_and_stats_structs_mirror_the_header():
     assert _c_struct_fields("qmg_route_options") == [f[0] for f in _abi.QmgRouteOptions._fields_]
     assert _c_struct_fields("qmg_route_stats") == [f[0] for f in _abi.QmgRouteStats._fields_]
     assert C.sizeof(_abi.QmgRouteOptions) == 8 * 4
-    assert C.sizeof(_abi.QmgRouteStats) == 64
+    assert C.sizeof(_abi.QmgRouteStats) == 72
 
 
 def test_bench_workloads_shard_disjointly():
