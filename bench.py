@@ -224,7 +224,7 @@ class WorkloadC4(Workload):
     circuit not at all."""
     key = "c4"
     n = 127
-    default_batch = 8192
+    default_batch = 16384
 
     def __init__(self, args):
         super().__init__(args)
