@@ -476,6 +476,29 @@ def cpu_baseline_for(wl, cores):
     return cb, r
 
 
+def build_instances(L, wl, n, cfg, seeds):
+    """The instances `seeds` of workload `wl` as the mapper sees them: the
+    concatenated gate lists (offsets, control, target), their layers
+    (routing.CircuitBatch) and one routing.RouteItem each."""
+    from qmap_b200 import routing
+    gl = [wl.instance_gates(s) for s in seeds]
+    views = [mapper_view(g[1], g[2], n) for g in gl]
+    sizes = [len(v[0]) for v in views]
+    off = np.concatenate(([0], np.cumsum(sizes))).astype(np.uint64)
+    ctrl = np.ascontiguousarray(np.concatenate([v[0] for v in views]), dtype=np.int32)
+    tgt = np.ascontiguousarray(np.concatenate([v[1] for v in views]), dtype=np.int32)
+    cb = routing.CircuitBatch(L, n, off, ctrl, tgt, cfg.layering)
+    items = [routing.RouteItem(cb[i], views[i][2], int(gl[i][3])) for i in range(len(seeds))]
+    return cb, items, off, ctrl, tgt
+
+
+def emitted_swaps(out, cfg) -> int:
+    """results.output.swaps of the reference: the SWAPs emitted, i.e. not those
+    of the first layer unless swapOnFirstLayer (HeuristicMapper.cpp:369-384)."""
+    first = 0 if cfg.swap_on_first_layer or len(out.layer_n_swaps) == 0 else int(out.layer_n_swaps[0])
+    return len(out.swaps) - first
+
+
 def _traffic(key):
     """Measured per-launch figures of the routing kernel from the committed ncu
     capture (profiles/traffic.json): DRAM bytes, L2 bytes, L2 peak."""
@@ -502,15 +525,7 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu):
     seeds = list(shard_seeds(rank, world, B))
     # ---- the callers' gate lists (host arrays): not part of any timed region
     log(f"{wl.key}: {len(seeds)} gate lists")
-    gl = [wl.instance_gates(s) for s in seeds]
-    views = [mapper_view(g[1], g[2], n) for g in gl]
-    sizes = [len(v[0]) for v in views]
-    off = np.concatenate(([0], np.cumsum(sizes))).astype(np.uint64)
-    ctrl = np.ascontiguousarray(np.concatenate([v[0] for v in views]), dtype=np.int32)
-    tgt = np.ascontiguousarray(np.concatenate([v[1] for v in views]), dtype=np.int32)
-    passes = [int(g[3]) for g in gl]
-    cb = routing.CircuitBatch(L, n, off, ctrl, tgt, cfg.layering)
-    items = [routing.RouteItem(cb[i], views[i][2], passes[i]) for i in range(len(seeds))]
+    cb, items, off, ctrl, tgt = build_instances(L, wl, n, cfg, seeds)
     opts = _abi.QmgRouteOptions()
     wl.options(opts)
     # what routeCircuit consumes: per-layer SWAP lists + layouts (the per-call
@@ -589,12 +604,7 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu):
         sh = [s for s in r["seeds"] if s in idx]
         ge = np.array([outs[idx[s]].expanded_nodes_final_pass for s in sh])
         gg = np.array([outs[idx[s]].generated_nodes_final_pass for s in sh])
-        # results.output.swaps: the SWAPs emitted, i.e. not those of the first
-        # layer unless swapOnFirstLayer (HeuristicMapper.cpp:369-384)
-        def emitted(o):
-            first = 0 if cfg.swap_on_first_layer or len(o.layer_n_swaps) == 0 else int(o.layer_n_swaps[0])
-            return len(o.swaps) - first
-        gs = np.array([emitted(outs[idx[s]]) for s in sh])
+        gs = np.array([emitted_swaps(outs[idx[s]], cfg) for s in sh])
         pos = [r["seeds"].index(s) for s in sh]
         re_, rg, rs = r["expanded"][pos], r["generated"][pos], r["swaps"][pos]
         parity.update({

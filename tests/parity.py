@@ -54,6 +54,19 @@ def random_weighted(n, extra, seed, integer):
     return sorted(set(cm)), w
 
 
+def cheapest_path_architecture():
+    """The architecture of test_architecture.cpp:928-960: a path of nrEdges
+    unidirectional edges 0..nrEdges and a detour of nrEdges + 1 bidirectional
+    ones; nrEdges = 1 + ceil(30 / (34 - 30)) = 9."""
+    import math
+    nr = 1 + math.ceil(30 / (34 - 30))
+    cm = [(i + 1, i) for i in range(nr)]
+    for i in range(nr + 1, 2 * nr):
+        cm += [(i, i + 1), (i + 1, i)]
+    cm += [(0, nr + 1), (nr + 1, 0), (2 * nr, nr), (nr, 2 * nr)]
+    return 2 * nr + 1, sorted(set(cm)), nr
+
+
 def ref() -> refapi.Ref:
     global _ref
     if _ref is None:
@@ -122,11 +135,25 @@ def run_pair(backend, lib, ra, circ_path_or_circ, rel=0.0, **kw):
         rr = ref().map_qasm(ra, circ_path_or_circ, cfg_r)
     else:
         circ = circ_path_or_circ
-        c, t = circ.gate_arrays()
-        rr = ref().map_gates(ra, circ.n_qubits, c, t, cfg_r)
+        if circ.measurements:
+            # (measured qubits are not idle: the reference must see them)
+            import tempfile
+            with tempfile.NamedTemporaryFile("w", suffix=".qasm", delete=False) as f:
+                f.write(circ.to_qasm())
+            try:
+                rr = ref().map_qasm(ra, f.name, cfg_r)
+            finally:
+                os.unlink(f.name)
+        else:
+            c, t = circ.gate_arrays()
+            rr = ref().map_gates(ra, circ.n_qubits, c, t, cfg_r)
+    # room for the layers a split adds: the backend then splits layers itself
+    # exactly where the reference does (qmg_instance.layer_capacity)
+    split = bool((rr.call_flags & 2).any())
     out = routing.route_batch(backend, ra.n, cfg, [item_for(lib, ra.n, circ, cfg)],
-                              want_layer_qubits=True)[0]
-    return compare(out, rr, rel), out, rr
+                              want_layer_qubits=True,
+                              extra_layers=rr.n_layers if split else 0)[0]
+    return compare(out, rr, rel, allow_split=True), out, rr
 
 
 def cuda_backend_for(ra, arch=None):
@@ -259,3 +286,69 @@ def run_golden(backend, lib, n, g: GoldenRun, rel=0.0, backend_splits=True, opti
                               extra_layers=g.n_layers if g.meta["split"] and backend_splits
                               else 0)[0]
     return compare(out, g, rel, allow_split=True), out
+
+
+def fidelity_known_answers():
+    """The reference's fidelity-aware known-answer tests, re-expressed
+    (test/sc/heuristic/test_heuristic.cpp:1769-1851 RemapSingleQubit, :1853-1932
+    QubitRideAlong, :1934-1981 SingleQubitsCompete): architecture, error rates,
+    circuit (every qubit measured, so none is idle), expected SWAP count and
+    total log-fidelity cost.  One layer each (disjoint_2q_blocks), identity
+    layout, swapOnFirstLayer."""
+    import math
+
+    def c(e):
+        return -math.log2(1 - e)
+
+    def path(n):
+        return [(i, i + 1) for i in range(n - 1)] + [(i + 1, i) for i in range(n - 1)]
+
+    def sym(d):
+        return {**d, **{(b, a): r for (a, b), r in d.items()}}
+
+    e5, e4, e3, e1, e0 = 0.99, 0.9, 0.5, 0.1, 0.01
+    out = []
+    circ = qcirc.Circuit(6, measurements=[(i, i) for i in range(6)], n_clbits=6)
+    for _ in range(5):
+        circ.cx(2, 0)
+        circ.gate("x", 3)
+    out.append(dict(name="RemapSingleQubit", n=6, cm=path(6), q1=[e5, e5, e5, e4, e4, e1],
+                    cx=sym({(0, 1): e1, (1, 2): e3, (2, 3): e5, (3, 4): e0, (4, 5): e0}), circuit=circ,
+                    swaps=3, fidelity=3 * c(e3) + 3 * c(e0) + 3 * c(e0) + 5 * c(e1) + 5 * c(e1)))
+    circ = qcirc.Circuit(7, measurements=[(i, i) for i in range(7)], n_clbits=7)
+    for _ in range(5):
+        circ.cx(3, 0)
+        circ.cx(6, 4)
+    tree = [(0, 1), (1, 2), (2, 3), (1, 4), (2, 5), (5, 6)]
+    out.append(dict(name="QubitRideAlong", n=7, cm=tree + [(b, a) for a, b in tree], q1=[e5] * 7,
+                    cx=sym({(0, 1): e4, (1, 2): e3, (2, 3): e1, (1, 4): e1, (2, 5): e3, (5, 6): e4}),
+                    circuit=circ, swaps=4,
+                    fidelity=3 * c(e4) + 3 * c(e3) + 3 * c(e4) + 3 * c(e3) + 5 * c(e1) + 5 * c(e1)))
+    circ = qcirc.Circuit(3, measurements=[(i, i) for i in range(3)], n_clbits=3)
+    circ.gate("x", 0)
+    circ.gate("x", 2)
+    out.append(dict(name="SingleQubitsCompete", n=3, cm=path(3), q1=[0.8, 0.1, 0.8],
+                    cx=sym({(0, 1): 0.1, (1, 2): 0.1}), circuit=circ, swaps=1,
+                    fidelity=3 * c(0.1) + c(0.8) + c(0.1)))
+    return out
+
+
+FIDELITY_KNOWN_ANSWER_CONFIG = dict(layering="disjoint_2q_blocks", initial_layout="identity",
+                                    heuristic="fidelity_best_location", lookahead_heuristic="none",
+                                    pre_mapping_optimizations=False, post_mapping_optimizations=False,
+                                    swap_on_first_layer=True)
+
+
+def check_fidelity_known_answer(k, backend_for):
+    """backend_for(ra) -> (backend, lib); routes k's circuit and checks the
+    reference's expectations and the compiled reference's result."""
+    ra = ref().arch_create(k["n"], sorted(set(k["cm"])))
+    ra.set_error_rates(k["q1"], [k["cx"][tuple(int(x) for x in e)] for e in ra.edges])
+    be, lib = backend_for(ra, k)
+    msg, out, rr = run_pair(be, lib, ra, k["circuit"], **FIDELITY_KNOWN_ANSWER_CONFIG)
+    assert msg == "", (k["name"], msg)
+    assert rr.n_layers == 1 and rr.swaps == k["swaps"], k["name"]
+    assert abs(rr.total_log_fidelity - k["fidelity"]) <= 1e-6, k["name"]
+    assert len(out.swaps) == k["swaps"], k["name"]
+    # one layer: the result node's fixed cost is the whole circuit's cost
+    assert abs(out.layers[0]["cost_fixed"] - k["fidelity"]) <= 1e-6, k["name"]

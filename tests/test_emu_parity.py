@@ -169,3 +169,10 @@ def test_full_search_variant_matches_reference_outputs(env):
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.startswith("ok")
+
+
+@pytest.mark.parametrize("k", parity.fidelity_known_answers(), ids=lambda k: k["name"])
+def test_reference_fidelity_known_answers(k):
+    """test_heuristic.cpp:1769-1981 on the host build of the kernel source."""
+    parity.check_fidelity_known_answer(
+        k, lambda ra, _k: (lambda be: (be, be.lib))(emu_backend.EmuBackend.from_ref_arch(ra)))

@@ -111,3 +111,58 @@ def test_config3_suite_on_heavy_hex_27():
         if msg:
             bad.append((name, msg))
     assert not bad, bad[:5]
+
+
+def _bench_workload(key, **kw):
+    import argparse
+    import bench
+    args = argparse.Namespace(c4_cx=30, cpu_sample=0, searches_per_sm=0)
+    for k, v in kw.items():
+        setattr(args, k, v)
+    return bench, bench.WORKLOADS[key](args)
+
+
+@pytest.mark.parametrize("key,count", [("c4", 64), ("c3", 400), ("c2", 64)])
+def test_bench_workloads_instance_by_instance(key, count, monkeypatch):
+    """The very instances bench.py routes (seeds 0..count-1 of each config),
+    through the same batched createLayers and qmg_route_batch call, against the
+    compiled reference: expanded / generated nodes of the final pass and SWAPs
+    emitted per instance, and every routed circuit replayed by the verifier."""
+    # (config 4 asks for most of the HBM as node pools; not in a test)
+    monkeypatch.setenv("QMAP_B200_POOL_MB", "20000")
+    bench, wl = _bench_workload(key)
+    L = _abi.load()
+    a = wl.architecture(0)
+    n = a.n_qubits
+    cfg = wl.config()
+    seeds = list(range(count))
+    cb, items, off, ctrl, tgt = bench.build_instances(L, wl, n, cfg, seeds)
+    opts = _abi.QmgRouteOptions()
+    wl.options(opts)
+    be = routing.CudaBackend(L, a.handle)
+    b = routing.pack(n, items, lean=True)
+    be.route(cfg, b, opts)
+    outs = routing.unpack(b)
+    assert all(o.status == 0 for o in outs)
+    verdict = cb.verify(a.edges, b.res, len(items), fidelity_aware=cfg.heuristic == 4)
+    assert (verdict == 1).all(), np.nonzero(verdict != 1)[0][:10]
+    r = bench.run_reference(wl, seeds, min(16, bench.host_cores()))
+    assert np.array_equal([o.expanded_nodes_final_pass for o in outs], r["expanded"])
+    assert np.array_equal([o.generated_nodes_final_pass for o in outs], r["generated"])
+    assert np.array_equal([bench.emitted_swaps(o, cfg) for o in outs], r["swaps"])
+
+
+def test_verifier_rejects_a_corrupted_routing():
+    bench, wl = _bench_workload("c2")
+    L = _abi.load()
+    a = wl.architecture(0)
+    cfg = wl.config()
+    cb, items, *_ = bench.build_instances(L, wl, 16, cfg, [0, 1, 2, 3])
+    be = routing.CudaBackend(L, a.handle)
+    b = routing.pack(16, items, lean=True)
+    be.route(cfg, b)
+    assert (cb.verify(a.edges, b.res, 4) == 1).all()
+    b.swaps[1][3] = (5, 5)                      # a SWAP that is not on a coupling edge
+    b.lns[2][5] += 1                            # one SWAP too many in a layer
+    v = cb.verify(a.edges, b.res, 4)
+    assert v.tolist() == [1, 0, 0, 1]

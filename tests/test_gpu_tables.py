@@ -198,3 +198,39 @@ def test_fidelity_tables_random_calibration_grid_4x4(tmp_path, seed):
     got = a.fidelity_distance_tables()
     assert got.shape == want.shape
     assert np.array_equal(got, want)
+
+
+# ---- the reference's own Architecture tests (test/sc/test_architecture.cpp:274-960)
+def _arch_goldens():
+    import json
+    with open(os.path.join(parity.ROOT, "tests", "golden", "architecture_tests.json")) as f:
+        return json.load(f)["tests"]
+
+
+@pytest.mark.parametrize("g", _arch_goldens(), ids=lambda g: g["test"])
+def test_reference_architecture_tests_on_the_device(g):
+    from test_oracle import check_architecture_golden
+    props = ar.Properties()
+    for q, r in enumerate(g["single_qubit_error"]):
+        props.set_single_qubit_error_rate(q, "x", r)
+    for a_, b_, r in g["two_qubit_error"]:
+        props.set_two_qubit_error_rate(a_, b_, r)
+    a = ar.Architecture(g["n"], [tuple(e) for e in g["coupling_map"]], props)
+    check_architecture_golden(g, a.fidelity_distance_tables(), a.swap_fidelity_costs())
+    # and bit for bit what the compiled reference builds
+    ra = parity.ref().arch_create(g["n"], [tuple(e) for e in g["coupling_map"]])
+    rate = {(x, y): r for x, y, r in g["two_qubit_error"]}
+    ra.set_error_rates(g["single_qubit_error"], [rate[tuple(int(v) for v in e)] for e in ra.edges])
+    assert np.array_equal(a.fidelity_distance_tables(), ra.fidelity_distance_tables())
+
+
+def test_distance_cheapest_path_on_the_device():
+    """test_architecture.cpp:928-960; a mixed 30 / 34 architecture, so the table
+    comes from the replay of the reference's Dijkstra (K1')."""
+    n, cm, nr = parity.cheapest_path_architecture()
+    a = ar.Architecture(n, cm)
+    d = a.distance_table(True)
+    assert d.shape == (n, n) and abs(d[0][nr] - nr * 30.0) <= 1e-6
+    ra = parity.ref().arch_create(n, cm)
+    assert np.array_equal(d, ra.distance_table(True))
+    assert np.array_equal(a.distance_table(False), ra.distance_table(False))

@@ -214,3 +214,45 @@ def test_random_circuits_against_compiled_reference(arch):
         if msg and "split" not in msg:
             bad.append((seed, kw, msg))
     assert not bad, bad[:3]
+
+
+# ---------------------------------------------------------------------------
+# the reference's own Architecture tests (test/sc/test_architecture.cpp:274-960)
+# ---------------------------------------------------------------------------
+def _arch_goldens():
+    import json
+    with open(os.path.join(parity.ROOT, "tests", "golden", "architecture_tests.json")) as f:
+        return json.load(f)["tests"]
+
+
+def check_architecture_golden(g, tables, swap_cost):
+    """tables: (K, n, n) k-edge-skip fidelity distance tables, swap_cost (n, n);
+    a table index >= K reads as all zero (Architecture.hpp:312-314)."""
+    n = g["n"]
+    for t in g["fidelity_distance_tables"]:
+        got = tables[t["skip"]] if t["skip"] < len(tables) else np.zeros((n, n))
+        np.testing.assert_allclose(got, np.array(t["table"]), rtol=0, atol=t["tol"],
+                                   err_msg=f"{g['test']} skip {t['skip']}")
+    src = {"swapFidCost": swap_cost, "fidDistance": tables[0]}
+    for e in g["near"]:
+        assert abs(src[e["what"]][e["i"]][e["j"]] - e["value"]) <= e["tol"], (g["test"], e)
+    for e in g["greater_than_1e20"]:
+        assert src[e["what"]][e["i"]][e["j"]] > 1e20, (g["test"], e)
+
+
+@pytest.mark.parametrize("g", _arch_goldens(), ids=lambda g: g["test"])
+def test_compiled_reference_reproduces_its_architecture_tests(g):
+    ra = parity.ref().arch_create(g["n"], [tuple(e) for e in g["coupling_map"]])
+    rate = {(a, b): r for a, b, r in g["two_qubit_error"]}
+    ra.set_error_rates(g["single_qubit_error"], [rate[tuple(int(x) for x in e)] for e in ra.edges])
+    check_architecture_golden(g, ra.fidelity_distance_tables(), ra.swap_fidelity_costs())
+
+
+def test_distance_cheapest_path_reference():
+    """test_architecture.cpp:928-960 (DistanceCheapestPathTest): 9 unidirectional
+    edges (34 each) lose against 10 bidirectional ones (30 each)."""
+    n, cm, nr = parity.cheapest_path_architecture()
+    ra = parity.ref().arch_create(n, cm)
+    d = ra.distance_table(True)
+    assert d.shape == (2 * nr + 1, 2 * nr + 1)
+    assert abs(d[0][nr] - nr * 30.0) <= 1e-6
