@@ -343,6 +343,20 @@ typedef struct {
   int32_t status; /* qmg_status of this layer */
 } qmg_layer_result;
 
+/* one generated search node as DataLogger::logSearchNode records it
+ * (src/sc/DataLogger.cpp:216-269: nodeId; parentId; costFixed; costHeur;
+ * lookaheadPenalty; validMapping; depth; qubits; swaps).  The node's layout and
+ * SWAP sequence follow from its ancestors and the layer's root layout
+ * (qmg_route_result.layer_root_qubits). */
+typedef struct {
+  double cost_fixed; /* costFixed + costFixedReversals, as logged */
+  double cost_heur;
+  double lookahead_penalty;
+  uint32_t id, parent, depth, layer;
+  uint16_t swap_first, swap_second; /* the SWAP that made the node */
+  uint16_t valid, root;
+} qmg_node_log_record;
+
 /* a logical qubit placed by mapUnmappedGates (HeuristicMapper.cpp:211-307) */
 typedef struct {
   uint16_t logical, physical;
@@ -388,6 +402,14 @@ typedef struct {
    * during pseudoRouteCircuit, HeuristicMapper.cpp:309-344) */
   uint64_t expanded_nodes_final_pass;
   uint64_t generated_nodes_final_pass;
+  /* optional (Configuration::dataLoggingPath, DataLogger.cpp:216-269): every
+   * node generated in the final routing pass, in generation order, and the
+   * root layout (qubits[]) of every layer, n entries per layer.  n_node_log is
+   * the number generated (more than node_log_capacity: the log is cut). */
+  qmg_node_log_record* node_log;
+  uint32_t node_log_capacity;
+  uint32_t n_node_log;
+  int16_t* layer_root_qubits;
 } qmg_route_result;
 
 /*

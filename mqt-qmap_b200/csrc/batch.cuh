@@ -21,6 +21,11 @@ struct qmg_batch {
   size_t nInst = 0;
   int n = 0;
   bool wantLayers = false, wantLayerQ = false, wantLayerNS = false;
+  bool wantNodeLog = false;
+  std::vector<uint32_t> logCap;
+  std::vector<uint64_t> logOff;
+  uint64_t totLogCap = 0;
+  size_t oNodeLog = 0, oRootQ = 0;
   // nLayers: layers of the instance's circuit; layerCap: rows of its
   // per-layer outputs (more when the device may split layers)
   std::vector<uint32_t> nLayers, layerCap, swapCap;
@@ -208,6 +213,8 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->layerOff.resize(nInst);
   b->swapCap.resize(nInst);
   b->swapOff.resize(nInst);
+  b->logCap.assign(nInst, 0);
+  b->logOff.assign(nInst, 0);
   for (size_t i = 0; i < nInst; ++i) {
     const auto& c = circs[circOf[i]];
     b->nLayers[i] = c.nLayers;
@@ -225,7 +232,13 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       b->wantLayers = b->wantLayers || capacities[i].layers != nullptr;
       b->wantLayerQ = b->wantLayerQ || capacities[i].layer_qubits != nullptr;
       b->wantLayerNS = b->wantLayerNS || capacities[i].layer_n_swaps != nullptr;
+      if (capacities[i].node_log != nullptr && capacities[i].node_log_capacity > 0) {
+        b->wantNodeLog = true;
+        b->logCap[i] = capacities[i].node_log_capacity;
+      }
     }
+    b->logOff[i] = b->totLogCap;
+    b->totLogCap += b->logCap[i];
     b->swapCap[i] = cap;
     b->swapOff[i] = b->totSwapCap;
     b->totSwapCap += cap;
@@ -351,6 +364,9 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   {
     const uint32_t v = opt != nullptr ? opt->search_variant : 0U;
     b->startFull = v == 1 || (v == 0 && cfg->heuristic >= 4 && n > 32) ? 1U : 0U;
+    if (b->wantNodeLog) {
+      b->startFull = 1;  // (the node log is written by the full variant)
+    }
   }
   uint32_t tableSize = 1;
   while (tableSize < 2 * poolNodes) {
@@ -395,6 +411,8 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->oLayerNS = lo.add(b->wantLayerNS ? b->totLayers * 2 : 0);
   b->oLayers = lo.add(b->wantLayers ? b->totLayers * sizeof(LayerOut) : 0);
   b->oLayerQ = lo.add(b->wantLayerQ ? b->totLayers * n * 2 : 0);
+  b->oNodeLog = lo.add(b->wantNodeLog ? b->totLogCap * sizeof(NodeLogRec) : 0);
+  b->oRootQ = lo.add(b->wantNodeLog ? b->totLayers * n * 2 : 0);
   b->oSwapsPacked = lo.add(b->totSwapCap * 4);
   const size_t pinnedOut = lo.size;
   b->oSwapsWork = lo.add(b->totSwapCap * 4);
@@ -613,6 +631,11 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
     I.finalQ = at<int16_t>(O, b->oFinalQ) + i * n;
     I.finalL = at<int16_t>(O, b->oFinalL) + i * n;
     I.startL = at<int16_t>(O, b->oStartL) + i * n;
+    if (b->wantNodeLog && b->logCap[i] > 0) {
+      I.nodeLog = at<NodeLogRec>(O, b->oNodeLog) + b->logOff[i];
+      I.nodeLogCap = b->logCap[i];
+      I.rootQ = at<int16_t>(O, b->oRootQ) + b->layerOff[i] * n;
+    }
     I.summary = at<uint32_t>(O, b->oSummary) + 8 * i;
     I.counters = at<uint64_t>(O, b->oCounters) + 4 * i;
   });
@@ -828,6 +851,16 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
     if (r.layer_qubits != nullptr && b->wantLayerQ) {
       std::memcpy(r.layer_qubits, at<int16_t>(Hh, b->oLayerQ) + b->layerOff[i] * n,
                   nl * n * 2);
+    }
+    r.n_node_log = summary[8 * i + 6];
+    if (b->wantNodeLog && b->logCap[i] > 0 && r.node_log != nullptr) {
+      const size_t k = std::min<size_t>({r.n_node_log, b->logCap[i], r.node_log_capacity});
+      std::memcpy(r.node_log, at<NodeLogRec>(Hh, b->oNodeLog) + b->logOff[i],
+                  k * sizeof(NodeLogRec));
+      if (r.layer_root_qubits != nullptr) {
+        std::memcpy(r.layer_root_qubits, at<int16_t>(Hh, b->oRootQ) + b->layerOff[i] * n,
+                    nl * n * 2);
+      }
     }
     if (r.swaps != nullptr) {
       const uint32_t ns = r.n_swaps_total;

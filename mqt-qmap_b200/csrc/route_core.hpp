@@ -149,6 +149,19 @@ struct LayerOut {  // == qmg_layer_result
   int32_t early, status;
 };
 
+// one generated search node as DataLogger::logSearchNode records it
+// (src/sc/DataLogger.cpp:216-269), == qmg_node_log_record.  The node's layout
+// and SWAP sequence follow from its ancestors' records and the layer's root
+// layout (InstView::rootQ).
+struct NodeLogRec {
+  double cost_fixed;  // costFixed + costFixedReversals
+  double cost_heur, lookahead_penalty;
+  uint32_t id, parent, depth, layer;
+  uint16_t swap_first, swap_second;  // the SWAP that made the node
+  uint16_t valid, root;
+};
+static_assert(sizeof(NodeLogRec) == 48, "NodeLogRec layout");
+
 struct InstView {
   CircView circ;
   const int16_t* initLoc;  // n or null
@@ -182,6 +195,11 @@ struct InstView {
   // routing pass only (what the reference's heuristicBenchmark counts: it
   // switches the counters off inside pseudoRouteCircuit, :309-344)
   uint64_t* counters;
+  // optional log of every node generated in the final pass, in generation
+  // order ([6] of summary = their number), and the root layout of every layer
+  NodeLogRec* nodeLog;
+  uint32_t nodeLogCap;
+  int16_t* rootQ;  // layerCap * n
 };
 
 // entries of one layout array in a node record: n rounded up to a multiple of
@@ -845,6 +863,8 @@ template <int H, bool kFull> struct Search {
   bool maskReady = false;
   bool allowSplit = false;  // this aStarMap call may stop at the split limit
   uint64_t totExpanded = 0, totGenerated = 0;
+  uint32_t nLog = 0;      // nodes logged so far (InstView::nodeLog)
+  uint32_t parentId = 0;  // Node::id of the node being expanded
   uint64_t pseudoExpanded = 0, pseudoGenerated = 0;  // of the pseudo passes
 
   QMG_HD Search(const ArchView& a, const CfgView& c, InstView& i,
@@ -1896,6 +1916,35 @@ template <int H, bool kFull> struct Search {
     g.sync();
   }
 
+  // DataLogger::logSearchNode for a generated node (final pass, full variant)
+  QMG_HD void logNode(const Child& ch, uint32_t id, uint32_t depth, bool root) {
+    if (!kFull || !record || I.nodeLog == nullptr) {
+      return;
+    }
+    if (g.lane == 0 && nLog < I.nodeLogCap) {
+      NodeLogRec r;
+      r.cost_fixed = ch.fixed + ch.rev;
+      r.cost_heur = ch.heur;
+      r.lookahead_penalty = ch.look;
+      r.id = id;
+      r.parent = root ? 0U : parentId;
+      r.depth = depth;
+      r.layer = layer;
+      r.swap_first = root ? static_cast<uint16_t>(0) : ch.a;
+      r.swap_second = root ? static_cast<uint16_t>(0) : ch.b;
+      r.valid = ch.valid;
+      r.root = root ? 1 : 0;
+      I.nodeLog[nLog] = r;
+    }
+    if (root && I.rootQ != nullptr) {
+      QMG_NOUNROLL
+      for (int i = g.lane; i < n; i += Group::W) {
+        I.rootQ[static_cast<size_t>(layer) * n + i] = pQ[i];
+      }
+    }
+    ++nLog;
+  }
+
   // UniquePriorityQueue::push :59-82 for one node.  Group-uniform.  Returns
   // false when the node pool is exhausted.  Only nodes in the open list take
   // part in the layout identity (pop erases the membership, :84-93), so short
@@ -1903,6 +1952,7 @@ template <int H, bool kFull> struct Search {
   QMG_HD bool push(const Child& ch, uint32_t parentIdx, uint32_t depth,
                    bool root) {
     const uint32_t id = nextId++;
+    logNode(ch, id, depth, root);
     return pushOne(ch, parentIdx, depth, root, id);
   }
   QMG_HD bool pushOne(const Child& ch, uint32_t parentIdx, uint32_t depth,
@@ -2116,6 +2166,7 @@ template <int H, bool kFull> struct Search {
       for (int j = 0; j < nj; ++j) {
         const Child ch = S.ch()[c0 + j];
         const uint32_t id = nextId++;
+        logNode(ch, id, depth, false);
         const uint32_t d = g.bcast(dec, j);
         if (d == kSkip) {
           continue;
@@ -2666,7 +2717,8 @@ template <int H, bool kFull> struct Search {
     enumDone = true;
     // the root's lookahead penalty is only reported, never compared, when the
     // root is a goal of a tight heuristic
-    const bool rootLookWanted = record && I.layers != nullptr;
+    const bool rootLookWanted =
+        record && (I.layers != nullptr || (kFull && I.nodeLog != nullptr));
     QMG_NOUNROLL
     for (;;) {
       // room for a chunk of new nodes: a private pool that is about to fill
@@ -2690,6 +2742,7 @@ template <int H, bool kFull> struct Search {
           if (goalRoot) {
             // the root is a goal and the heuristic is tight: the first pop
             // ends the search (:585-599) - no node record is needed
+            logNode(S.ch()[0], 0, 0, true);
             nextId = 1;
             st.solNodes = 1;
             st.rootResult = true;
@@ -2826,6 +2879,7 @@ template <int H, bool kFull> struct Search {
       parentHash = h->hash;
       depth = h->depth + 1;
       parent = cur;
+      parentId = h->id;
       enumCi = 0;
       enumK = 0;
       enumDone = false;
@@ -2896,7 +2950,7 @@ template <int H, bool kFull> struct Search {
   QMG_HD int routeLayerIn(uint32_t l, bool finalPass, bool reverse,
                           uint32_t& swapTotal) {
     const bool wantRec = finalPass && I.layers != nullptr;
-    if (!kFid && !wantRec) {
+    if (!kFid && !wantRec && !(kFull && I.nodeLog != nullptr)) {
       // a layer without 2q gates needs no search when no record of it is
       // wanted: nothing to place, the root (1 generated node) is the result
       if (ldc(I.circ.g2Off + l + 1) == ldc(I.circ.g2Off + l)) {
@@ -3176,6 +3230,7 @@ template <int H, bool kFull> struct Search {
       I.summary[1] = nPlace;
       I.summary[2] = doneLayers;
       I.summary[3] = static_cast<uint32_t>(rc);
+      I.summary[6] = nLog;
       I.counters[0] = totExpanded;
       I.counters[1] = totGenerated;
       I.counters[2] = totExpanded - pseudoExpanded;

@@ -88,6 +88,8 @@ class QmgRouteResult(C.Structure):
         ("split_layers", C.c_void_p), ("split_capacity", C.c_uint32),
         ("n_splits", C.c_uint32),
         ("expanded_nodes_final_pass", C.c_uint64), ("generated_nodes_final_pass", C.c_uint64),
+        ("node_log", C.c_void_p), ("node_log_capacity", C.c_uint32), ("n_node_log", C.c_uint32),
+        ("layer_root_qubits", C.c_void_p),
     ]
 
 
@@ -129,6 +131,12 @@ LAYER_RESULT_DTYPE = np.dtype([
     ("early_termination", "i4"), ("status", "i4"),
 ])
 assert LAYER_RESULT_DTYPE.itemsize == 120
+NODE_LOG_DTYPE = np.dtype([
+    ("cost_fixed", "f8"), ("cost_heur", "f8"), ("lookahead_penalty", "f8"),
+    ("id", "u4"), ("parent", "u4"), ("depth", "u4"), ("layer", "u4"),
+    ("swap_first", "u2"), ("swap_second", "u2"), ("valid", "u2"), ("root", "u2"),
+])
+assert NODE_LOG_DTYPE.itemsize == 48
 
 # every symbol include/qmap_b200.h declares
 EXPORTS = [

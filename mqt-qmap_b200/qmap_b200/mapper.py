@@ -104,6 +104,12 @@ class HeuristicMapper:
         return loc
 
     # ------------------------------------------------------------------
+    # Configuration::dataLoggingPath (Configuration.hpp:53): a directory that
+    # receives nodes_layer_<i>.csv in the DataLogger's schema (DataLogger.cpp:
+    # 216-269) for the final routing pass; None = no logging
+    data_logging_path = None
+    node_log_capacity = 1 << 20
+
     def map(self, config=None, **kwargs) -> MappingResults:
         """HeuristicMapper::map (:44-107).
 
@@ -161,8 +167,12 @@ class HeuristicMapper:
         splits = 0
         while True:
             item = routing.RouteItem(lc, init, passes, first_layer=first)
+            log_cap = self.node_log_capacity if self.data_logging_path else 0
             out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True, lean=True,
-                                      extra_layers=extra)[0]
+                                      extra_layers=extra, node_log_capacity=log_cap)[0]
+            if log_cap and out.status == _abi.QMG_OK and first == 0:
+                from . import datalog
+                datalog.write_node_logs(self.data_logging_path, out)
             if out.split_layers is not None and len(out.split_layers):
                 lc = lc.split_copy(out.split_layers)
                 splits += len(out.split_layers)

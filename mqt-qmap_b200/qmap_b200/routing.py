@@ -13,7 +13,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _abi
-from ._abi import (LAYER_RESULT_DTYPE, QmgConfig, QmgInstance, QmgLayers,
+from ._abi import (LAYER_RESULT_DTYPE, NODE_LOG_DTYPE, QmgConfig, QmgInstance, QmgLayers,
                    QmgRouteOptions, QmgRouteResult, QmgRouteStats, QmapError)
 
 
@@ -237,6 +237,9 @@ class RouteOutput:
     layer_qubits: np.ndarray | None = None
     layer_n_swaps: np.ndarray | None = None  # uint16 per layer
     split_layers: np.ndarray | None = None  # layers split by the backend (final pass)
+    node_log: np.ndarray | None = None  # NODE_LOG_DTYPE, generation order (final pass)
+    n_node_log: int = 0  # nodes generated (more than len(node_log): the log was cut)
+    layer_root_qubits: np.ndarray | None = None  # (layers, n): root layout of every layer
     expanded_nodes_final_pass: int = 0  # the reference's heuristicBenchmark counters
     generated_nodes_final_pass: int = 0
     _offsets: np.ndarray | None = None
@@ -267,11 +270,13 @@ class BatchBuffers:
     lns: list = field(default_factory=list)
     keep: list = field(default_factory=list)
     layer_cap: list = field(default_factory=list)  # per-instance rows of layers/lq/lns
+    node_logs: list = field(default_factory=list)
+    root_q: list = field(default_factory=list)
     split_logs: list = field(default_factory=list)
 
 
 def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False,
-         extra_layers=0) -> BatchBuffers:
+         extra_layers=0, node_log_capacity=0) -> BatchBuffers:
     """lean: no per-layer qmg_layer_result records, only the compact per-layer
     SWAP counts (what circuit emission needs).  extra_layers: additional rows
     in the per-layer outputs; with extra_layers > 0 the backend splits layers
@@ -326,6 +331,15 @@ def pack(n: int, items, want_layer_qubits=False, swap_capacity=None, lean=False,
         r.final_qubits = b.fq[i].ctypes.data
         r.final_locations = b.fl[i].ctypes.data
         r.start_locations = b.sl[i].ctypes.data
+        if node_log_capacity > 0:
+            # DataLogger-style log of every generated node (final pass)
+            nlog = np.zeros(node_log_capacity, dtype=NODE_LOG_DTYPE)
+            rq = np.full((cap_l, n), -1, dtype=np.int16)
+            b.node_logs.append(nlog)
+            b.root_q.append(rq)
+            r.node_log = nlog.ctypes.data
+            r.node_log_capacity = node_log_capacity
+            r.layer_root_qubits = rq.ctypes.data
         if want_layer_qubits:
             lq = np.full((cap_l, n), -1, dtype=np.int16)
             b.lq.append(lq)
@@ -347,6 +361,10 @@ def unpack(b: BatchBuffers) -> list:
             placements=b.places[i][: int(r.n_placements_total)],
             final_qubits=b.fq[i], final_locations=b.fl[i], start_locations=b.sl[i],
             layer_qubits=b.lq[i][:nl] if b.lq else None,
+            node_log=(b.node_logs[i][: min(int(r.n_node_log), len(b.node_logs[i]))]
+                      if b.node_logs else None),
+            n_node_log=int(r.n_node_log),
+            layer_root_qubits=b.root_q[i][:nl] if b.root_q else None,
             expanded_nodes_final_pass=int(r.expanded_nodes_final_pass),
             generated_nodes_final_pass=int(r.generated_nodes_final_pass),
             split_layers=(b.split_logs[i][: min(int(r.n_splits), len(b.split_logs[i]))]
@@ -370,12 +388,13 @@ class CudaBackend:
 
 
 def route_batch(backend, n: int, cfg: QmgConfig, items, want_layer_qubits=False,
-                options=None, max_retries=6, lean=False, extra_layers=0) -> list:
+                options=None, max_retries=6, lean=False, extra_layers=0,
+                node_log_capacity=0) -> list:
     """Route `items` (RouteItem) and return one RouteOutput per item.  Swap
     buffers that turn out too small are grown and the batch is re-run."""
     cap = None
     for _ in range(max_retries):
-        b = pack(n, items, want_layer_qubits, cap, lean, extra_layers)
+        b = pack(n, items, want_layer_qubits, cap, lean, extra_layers, node_log_capacity)
         if options is not None:
             backend.route(cfg, b, options)
         else:

@@ -272,23 +272,29 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     I.finalL = r.final_locations;
     I.startL = r.start_locations;
     I.layerQ = r.layer_qubits;
+    I.nodeLog = reinterpret_cast<NodeLogRec*>(r.node_log);
+    I.nodeLogCap = r.node_log != nullptr ? r.node_log_capacity : 0;
+    I.rootQ = r.layer_root_qubits;
     uint32_t summary[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     I.layerNSwaps = r.layer_n_swaps;
     uint64_t counters[4] = {0, 0, 0, 0};
     I.summary = summary;
     I.counters = counters;
+    // (a node log is written by the full variant only)
+    const bool sf = startFull || I.nodeLog != nullptr;
     switch (C.heuristic) {
-    case 0: { runBoth<0>(A, C, I, M, S, startFull); break; }
-    case 1: { runBoth<1>(A, C, I, M, S, startFull); break; }
-    case 2: { runBoth<2>(A, C, I, M, S, startFull); break; }
-    case 3: { runBoth<3>(A, C, I, M, S, startFull); break; }
-    default: { runBoth<4>(A, C, I, M, S, startFull); break; }
+    case 0: { runBoth<0>(A, C, I, M, S, sf); break; }
+    case 1: { runBoth<1>(A, C, I, M, S, sf); break; }
+    case 2: { runBoth<2>(A, C, I, M, S, sf); break; }
+    case 3: { runBoth<3>(A, C, I, M, S, sf); break; }
+    default: { runBoth<4>(A, C, I, M, S, sf); break; }
     }
     stamp = M.stamp;
     r.n_swaps_total = summary[0];
     r.n_placements_total = summary[1];
     r.n_layers_done = summary[2];
     r.n_splits = summary[5];
+    r.n_node_log = summary[6];
     r.status = static_cast<int32_t>(summary[3]);
     r.expanded_nodes = counters[0];
     r.generated_nodes = counters[1];

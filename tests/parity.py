@@ -352,3 +352,56 @@ def check_fidelity_known_answer(k, backend_for):
     assert len(out.swaps) == k["swaps"], k["name"]
     # one layer: the result node's fixed cost is the whole circuit's cost
     assert abs(out.layers[0]["cost_fixed"] - k["fidelity"]) <= 1e-6, k["name"]
+
+
+# ---------------------------------------------------------------------------
+# DataLogger parity (src/sc/DataLogger.cpp:216-269) and the reference's
+# HeuristicProperties checks (test/sc/heuristic/test_heuristic.cpp:584-775)
+# ---------------------------------------------------------------------------
+# the fixture's settings (test_heuristic.cpp:261-268)
+DATALOG_CONFIG = dict(debug=True, automatic_layer_splits=False, initial_layout="identity",
+                      layering="disjoint_2q_blocks", lookahead_heuristic="none")
+DATALOG_CIRCUITS = ["3_17_13", "ex-1_166", "ham3_102", "miller_11", "4gt11_84", "4mod5-v0_20", "mod5d1_63"]
+
+
+def check_node_log(backend, lib, arch_file, calib, circuit, heuristic, node_log_capacity=200000):
+    """Routes `circuit` with a node log and compares it, file by file and line
+    by line, with what the compiled reference's DataLogger writes; then the
+    reference's property checks on the log.  Returns the number of nodes."""
+    import tempfile
+    from qmap_b200 import datalog
+    ra = ref().arch_load(os.path.join(ARCHS, arch_file), os.path.join(ARCHS, calib) if calib else None)
+    kw = dict(DATALOG_CONFIG, heuristic=heuristic)
+    path = os.path.join(CIRCUITS, circuit + ".qasm")
+    d = tempfile.mkdtemp(prefix="qmap_datalog_") + os.sep
+    rr = ref().map_qasm(ra, path, refapi.make_config(**kw), d)
+    cfg = routing.make_config(**kw)
+    circ = qcirc.load_qasm(path)
+    out = routing.route_batch(backend, ra.n, cfg, [item_for(lib, ra.n, circ, cfg)],
+                              want_layer_qubits=True, node_log_capacity=node_log_capacity)[0]
+    assert out.status == 0
+    assert compare(out, rr) == ""
+    lines = datalog.layer_lines(out, rr.n_layers)
+    total = 0
+    tight = heuristic != 4  # isTight (Heuristic.hpp:96-110)
+    for l in range(rr.n_layers):
+        want = open(os.path.join(d, f"nodes_layer_{l}.csv")).read().splitlines()
+        assert lines[l] == want, (circuit, arch_file, heuristic, l,
+                                  next((a, b) for a, b in zip(lines[l] + [""], want + [""]) if a != b))
+        total += len(want)
+        # ---- test_heuristic.cpp:652-775 on the device's log
+        nodes = {int(r["id"]): r for r in out.node_log if int(r["layer"]) == l}
+        final = nodes[int(out.layers[l]["result_node_id"])]
+        assert final["valid"] == 1
+        if tight:
+            assert abs(final["cost_heur"]) <= 1e-6   # tightness: goal nodes have h = 0
+        assert final["lookahead_penalty"] == 0
+        if heuristic in (0, 2, 3):  # isPrincipallyAdmissible (Heuristic.hpp:50-72)
+            k = final
+            while True:   # along the solution path f <= cost of the solution
+                assert k["cost_fixed"] + k["cost_heur"] <= final["cost_fixed"] + 1e-6
+                if k["root"]:
+                    break
+                k = nodes[int(k["parent"])]
+    assert total == sum(int(x) for x in out.layers["generated_nodes"])
+    return total

@@ -176,3 +176,22 @@ def test_reference_fidelity_known_answers(k):
     """test_heuristic.cpp:1769-1981 on the host build of the kernel source."""
     parity.check_fidelity_known_answer(
         k, lambda ra, _k: (lambda be: (be, be.lib))(emu_backend.EmuBackend.from_ref_arch(ra)))
+
+
+@pytest.mark.parametrize("arch,calib,heuristics", [
+    ("ibmq_yorktown.arch", None, [0, 1, 2, 3]),
+    ("ibmq_london.arch", "ibmq_london.csv", [0, 3, 4]),
+    ("ibm_qx5.arch", None, [0, 2]),
+])
+def test_node_log_equals_the_reference_datalogger(arch, calib, heuristics):
+    """Row f3: every generated node of the HeuristicProperties fixture runs
+    (test_heuristic.cpp:224-775), in the DataLogger's CSV schema, equal to the
+    files the compiled reference writes."""
+    ra = parity.ref().arch_load(os.path.join(parity.ARCHS, arch),
+                                os.path.join(parity.ARCHS, calib) if calib else None)
+    be = emu_backend.EmuBackend.from_ref_arch(ra, pool_nodes=1 << 17)
+    total = 0
+    for circuit in parity.DATALOG_CIRCUITS:
+        for h in heuristics:
+            total += parity.check_node_log(be, be.lib, arch, calib, circuit, h)
+    assert total > 300

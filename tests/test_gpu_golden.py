@@ -294,3 +294,29 @@ def test_batch_with_layer_splits_against_oracle():
                         (w.expanded_nodes, w.generated_nodes), key
                     nsplit += len(w.split_layers)
                 assert nsplit > 0, (arch, heur, passes)
+
+
+@pytest.mark.parametrize("arch,calib,heuristics,circuits", [
+    ("ibmq_yorktown.arch", None, [0, 1, 2, 3], parity.DATALOG_CIRCUITS),
+    ("ibmq_london.arch", "ibmq_london.csv", [0, 4], parity.DATALOG_CIRCUITS),
+    ("ibm_qx5.arch", None, [0, 1, 2, 3], parity.DATALOG_CIRCUITS + ["ising_model_10", "rd73_140"]),
+])
+def test_node_log_equals_the_reference_datalogger(arch, calib, heuristics, circuits):
+    """Row f3 on the device: every node generated in the HeuristicProperties
+    fixture runs (test/sc/heuristic/test_heuristic.cpp:224-775; 9 circuits,
+    IBM Yorktown / London with calibration / QX5), written in the DataLogger's
+    CSV schema (src/sc/DataLogger.cpp:216-269), equals the files the compiled
+    reference writes; the fixture's property checks run on the device's log."""
+    from qmap_b200 import architecture as ar2
+    a = ar2.Architecture().load_coupling_map(os.path.join(parity.ARCHS, arch))
+    if calib:
+        a.load_properties(os.path.join(parity.ARCHS, calib))
+    lib = _abi.load()
+    be = routing.CudaBackend(lib, a.handle)
+    total = 0
+    for circuit in circuits:
+        if qcirc.load_qasm(os.path.join(parity.CIRCUITS, circuit + ".qasm")).n_qubits > a.n_qubits:
+            continue
+        for h in heuristics:
+            total += parity.check_node_log(be, lib, arch, calib, circuit, h)
+    assert total > 300
