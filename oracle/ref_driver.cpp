@@ -15,6 +15,17 @@
 
 #include "../include/qmap_b200.h"
 
+// -DQMAP_DROPIN: the same driver around the GPU drop-in (integration/
+// GpuHeuristicMapper.hpp) instead of the reference's HeuristicMapper; built
+// into oracle/_ref/libqmapdropin.so, which links libqmap_b200.so.  Used by
+// tests/test_gpu_dropin.py only.
+#ifdef QMAP_DROPIN
+#include "../integration/GpuHeuristicMapper.hpp"
+using BaseMapper = GpuHeuristicMapper;
+#else
+using BaseMapper = HeuristicMapper;
+#endif
+
 #include <chrono>
 #include <cstring>
 #include <memory>
@@ -32,9 +43,9 @@ struct CallRecord {
   std::int32_t split = 0; // this call recursed after a layer split
 };
 
-class TracingMapper : public HeuristicMapper {
+class TracingMapper : public BaseMapper {
 public:
-  using HeuristicMapper::HeuristicMapper;
+  using BaseMapper::BaseMapper;
   std::vector<CallRecord> calls;
   std::vector<std::int16_t> qubitsBefore; // calls.size() * n
   std::vector<std::int16_t> qubitsAfter;
@@ -49,7 +60,7 @@ public:
     const bool fin = results.config.debug || inFinalPass();
     ++depth;
     const auto nestedBefore = calls.size();
-    Node res = HeuristicMapper::aStarMap(layer, reverse);
+    Node res = BaseMapper::aStarMap(layer, reverse);
     --depth;
     CallRecord c;
     c.layer = static_cast<std::uint32_t>(layer);
