@@ -410,6 +410,15 @@ typedef struct {
   uint32_t node_log_capacity;
   uint32_t n_node_log;
   int16_t* layer_root_qubits;
+  /* optional: every placement of every pass (the pseudo-routing passes too),
+   * in the order mapUnmappedGates made them; `physical` has bit 15 set when
+   * the qubit was placed by the 1q-gate rule of the fidelity-aware mapper
+   * (HeuristicMapper.cpp:213-231), which does not touch the mapped circuit's
+   * initialLayout / outputPermutation (the 2q rules do, :275-306).  Capacity
+   * n suffices: a qubit is placed once. */
+  qmg_placement* placement_log;
+  uint32_t placement_log_capacity;
+  uint32_t n_placement_log;
 } qmg_route_result;
 
 /*

@@ -127,6 +127,17 @@ private:
       throw QMAPException(std::string("qmap_b200: ") + qmg_last_error());
     }
   }
+  // (HeuristicMapper.cpp:196-208, findAndSWAP, for both permutations)
+  void moveInLayouts(qc::Qubit logical, qc::Qubit physical) {
+    for (qc::Permutation* map : {&qcMapped.initialLayout, &qcMapped.outputPermutation}) {
+      for (const auto& q : *map) {
+        if (q.second == logical) {
+          std::swap(map->at(physical), map->at(q.first));
+          break;
+        }
+      }
+    }
+  }
   static std::vector<double> flat(const Matrix& m) {
     std::vector<double> v;
     v.reserve(m.size() * m.size());
@@ -220,6 +231,7 @@ private:
       std::vector<std::int16_t> fq(n), fl(n);
       std::vector<qmg_placement> places(n);
       std::vector<std::uint32_t> splitLog(cap - nL + 1);
+      std::vector<qmg_placement> placeLog(n);
       qmg_route_result r{};
       r.layers = rec_.data();
       r.swaps = swaps_.data();
@@ -231,6 +243,8 @@ private:
       r.layer_qubits = layerQ_.data();
       r.split_layers = splitLog.data();
       r.split_capacity = static_cast<std::uint32_t>(cap - nL);
+      r.placement_log = placeLog.data();
+      r.placement_log_capacity = n;
       qmg_route_stats st{};
       check(qmg_route_batch(arch_, &cfg, 1, &inst, &r, nullptr, &st));
       if (r.status == QMG_BUFFER_TOO_SMALL && attempt < 6) {
@@ -240,6 +254,15 @@ private:
       check(r.status);
       secondsPerExpandedNode_ =
           r.expanded_nodes > 0 ? 1e-3 * st.kernel_ms / static_cast<double>(r.expanded_nodes) : 0.;
+      // mapUnmappedGates / mapToMinDistance also move the placed qubit in the
+      // mapped circuit's initialLayout and outputPermutation (:275-278,
+      // :304-306; not for the 1q-gate rule, :213-231): every placement of
+      // every pass, in order
+      for (std::uint32_t k = 0; k < r.n_placement_log && k < n; ++k) {
+        if ((placeLog[k].physical & 0x8000U) == 0) {
+          moveInLayouts(placeLog[k].logical, placeLog[k].physical);
+        }
+      }
       // the host's layers follow the splits of the final pass
       for (std::uint32_t k = 0; k < r.n_splits; ++k) {
         splitLayer(splitLog[k], *architecture);

@@ -21,7 +21,8 @@ struct qmg_batch {
   size_t nInst = 0;
   int n = 0;
   bool wantLayers = false, wantLayerQ = false, wantLayerNS = false;
-  bool wantNodeLog = false;
+  bool wantNodeLog = false, wantPlaceLog = false;
+  size_t oPlaceLog = 0;
   std::vector<uint32_t> logCap;
   std::vector<uint64_t> logOff;
   uint64_t totLogCap = 0;
@@ -232,6 +233,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       b->wantLayers = b->wantLayers || capacities[i].layers != nullptr;
       b->wantLayerQ = b->wantLayerQ || capacities[i].layer_qubits != nullptr;
       b->wantLayerNS = b->wantLayerNS || capacities[i].layer_n_swaps != nullptr;
+      b->wantPlaceLog = b->wantPlaceLog || capacities[i].placement_log != nullptr;
       if (capacities[i].node_log != nullptr && capacities[i].node_log_capacity > 0) {
         b->wantNodeLog = true;
         b->logCap[i] = capacities[i].node_log_capacity;
@@ -364,8 +366,8 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   {
     const uint32_t v = opt != nullptr ? opt->search_variant : 0U;
     b->startFull = v == 1 || (v == 0 && cfg->heuristic >= 4 && n > 32) ? 1U : 0U;
-    if (b->wantNodeLog) {
-      b->startFull = 1;  // (the node log is written by the full variant)
+    if (b->wantNodeLog || b->wantPlaceLog) {
+      b->startFull = 1;  // (the logs are written by the full variant)
     }
   }
   uint32_t tableSize = 1;
@@ -407,6 +409,7 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
   b->oStartL = lo.add(nInst * n * 2);
   b->oPlaces = lo.add(nInst * n * 4);
   b->oSplitLog = lo.add(b->totSplitCap * 4);
+  b->oPlaceLog = lo.add(b->wantPlaceLog ? nInst * n * 4 : 0);
   b->oSmallEnd = lo.size;
   b->oLayerNS = lo.add(b->wantLayerNS ? b->totLayers * 2 : 0);
   b->oLayers = lo.add(b->wantLayers ? b->totLayers * sizeof(LayerOut) : 0);
@@ -636,6 +639,10 @@ int batchCreate(const qmg_arch* arch, const qmg_config* cfg, size_t nInst,
       I.nodeLogCap = b->logCap[i];
       I.rootQ = at<int16_t>(O, b->oRootQ) + b->layerOff[i] * n;
     }
+    if (b->wantPlaceLog) {
+      I.placeLog = at<uint16_t>(O, b->oPlaceLog) + 2 * i * n;
+      I.placeLogCap = static_cast<uint32_t>(n);
+    }
     I.summary = at<uint32_t>(O, b->oSummary) + 8 * i;
     I.counters = at<uint64_t>(O, b->oCounters) + 4 * i;
   });
@@ -853,6 +860,11 @@ int batchFetch(qmg_batch* b, qmg_route_result* results, qmg_route_stats* stats) 
                   nl * n * 2);
     }
     r.n_node_log = summary[8 * i + 6];
+    r.n_placement_log = summary[8 * i + 7];
+    if (b->wantPlaceLog && r.placement_log != nullptr) {
+      const size_t k = std::min<size_t>({r.n_placement_log, n, r.placement_log_capacity});
+      std::memcpy(r.placement_log, at<uint16_t>(Hh, b->oPlaceLog) + 2 * i * n, k * 4);
+    }
     if (b->wantNodeLog && b->logCap[i] > 0 && r.node_log != nullptr) {
       const size_t k = std::min<size_t>({r.n_node_log, b->logCap[i], r.node_log_capacity});
       std::memcpy(r.node_log, at<NodeLogRec>(Hh, b->oNodeLog) + b->logOff[i],

@@ -200,6 +200,13 @@ struct InstView {
   NodeLogRec* nodeLog;
   uint32_t nodeLogCap;
   int16_t* rootQ;  // layerCap * n
+  // optional: every placement of every pass (pseudo-routing passes too), in
+  // order ([7] of summary = their number); the physical qubit has bit 15 set
+  // when the qubit was placed by the 1q-gate rule of the fidelity-aware
+  // mapper (:213-231), which - unlike the 2q rules - leaves the circuit's
+  // initialLayout / outputPermutation alone
+  uint16_t* placeLog;
+  uint32_t placeLogCap;
 };
 
 // entries of one layout array in a node record: n rounded up to a multiple of
@@ -2330,7 +2337,16 @@ template <int H, bool kFull> struct Search {
   uint32_t nPlace = 0;  // running count into I.places
   bool record = false;
 
-  QMG_HD void place(int logical, int phys) {
+  uint32_t nPlaceLog = 0;
+  QMG_HD void place(int logical, int phys, bool oneQubitRule = false) {
+    if (kFull && I.placeLog != nullptr) {
+      if (g.lane == 0 && nPlaceLog < I.placeLogCap) {
+        I.placeLog[2 * nPlaceLog] = static_cast<uint16_t>(logical);
+        I.placeLog[2 * nPlaceLog + 1] =
+            static_cast<uint16_t>(phys | (oneQubitRule ? 0x8000 : 0));
+      }
+      ++nPlaceLog;
+    }
     if (g.lane == 0) {
       S.curQ()[phys] = static_cast<int16_t>(logical);
       S.curL()[logical] = static_cast<int16_t>(phys);
@@ -2388,7 +2404,7 @@ template <int H, bool kFull> struct Search {
         if (S.curL()[e.q] == -1) {
           const int p = firstFree();
           if (p >= 0) {
-            place(e.q, p);
+            place(e.q, p, true);
           }
         }
       }
@@ -3231,6 +3247,7 @@ template <int H, bool kFull> struct Search {
       I.summary[2] = doneLayers;
       I.summary[3] = static_cast<uint32_t>(rc);
       I.summary[6] = nLog;
+      I.summary[7] = nPlaceLog;
       I.counters[0] = totExpanded;
       I.counters[1] = totGenerated;
       I.counters[2] = totExpanded - pseudoExpanded;

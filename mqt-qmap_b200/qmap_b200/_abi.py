@@ -90,6 +90,8 @@ class QmgRouteResult(C.Structure):
         ("expanded_nodes_final_pass", C.c_uint64), ("generated_nodes_final_pass", C.c_uint64),
         ("node_log", C.c_void_p), ("node_log_capacity", C.c_uint32), ("n_node_log", C.c_uint32),
         ("layer_root_qubits", C.c_void_p),
+        ("placement_log", C.c_void_p), ("placement_log_capacity", C.c_uint32),
+        ("n_placement_log", C.c_uint32),
     ]
 
 

@@ -275,13 +275,15 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     I.nodeLog = reinterpret_cast<NodeLogRec*>(r.node_log);
     I.nodeLogCap = r.node_log != nullptr ? r.node_log_capacity : 0;
     I.rootQ = r.layer_root_qubits;
+    I.placeLog = reinterpret_cast<uint16_t*>(r.placement_log);
+    I.placeLogCap = r.placement_log != nullptr ? r.placement_log_capacity : 0;
     uint32_t summary[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     I.layerNSwaps = r.layer_n_swaps;
     uint64_t counters[4] = {0, 0, 0, 0};
     I.summary = summary;
     I.counters = counters;
     // (a node log is written by the full variant only)
-    const bool sf = startFull || I.nodeLog != nullptr;
+    const bool sf = startFull || I.nodeLog != nullptr || I.placeLog != nullptr;
     switch (C.heuristic) {
     case 0: { runBoth<0>(A, C, I, M, S, sf); break; }
     case 1: { runBoth<1>(A, C, I, M, S, sf); break; }
@@ -295,6 +297,7 @@ QMG_API int qemu_route_batch(const qemu_arch* arch, const qmg_config* cfg,
     r.n_layers_done = summary[2];
     r.n_splits = summary[5];
     r.n_node_log = summary[6];
+    r.n_placement_log = summary[7];
     r.status = static_cast<int32_t>(summary[3]);
     r.expanded_nodes = counters[0];
     r.generated_nodes = counters[1];

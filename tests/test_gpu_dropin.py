@@ -62,7 +62,7 @@ def test_golden_runs_through_the_compiled_drop_in(dropin):
         key = (m["arch"], m["calibration"])
         if key not in archs:
             files = (os.path.join(parity.ARCHS, m["arch"] + ".arch"),
-                     os.path.join(parity.ARCHS, m["calibration"] + ".csv") if m["calibration"] else None)
+                     os.path.join(parity.ARCHS, m["calibration"]) if m["calibration"] else None)
             archs[key] = (R.arch_load(*files), dropin.arch_load(*files))
         ra, da = archs[key]
         cfg = refapi.make_config(debug=True, **m["config"])
@@ -73,10 +73,11 @@ def test_golden_runs_through_the_compiled_drop_in(dropin):
 
 
 def test_drop_in_throws_like_the_reference(dropin):
-    """InvalidCircuits (test_heuristic.cpp:951-968): a disconnected
-    architecture makes the search run dry -> QMAPException."""
-    cm = [(0, 1), (1, 0), (2, 3), (3, 2)]
-    da = dropin.arch_create(4, cm)
-    with pytest.raises(RuntimeError, match="No viable mapping found"):
-        dropin.map_gates(da, 4, np.array([0], dtype=np.int32), np.array([2], dtype=np.int32),
-                         refapi.make_config(initial_layout="identity"))
+    """InvalidCircuits (test_heuristic.cpp:951-960): cx(0,1) on a 2-qubit
+    architecture without any edge makes the search run dry -> QMAPException
+    "No viable mapping found." from either mapper."""
+    c, t = np.array([0], dtype=np.int32), np.array([1], dtype=np.int32)
+    for lib in (parity.ref(), dropin):
+        a = lib.arch_create(2, [])
+        with pytest.raises(RuntimeError, match="No viable mapping found"):
+            lib.map_gates(a, 2, c, t, refapi.make_config())
