@@ -499,6 +499,59 @@ def emitted_swaps(out, cfg) -> int:
     return len(out.swaps) - first
 
 
+# ---------------------------------------------------------------------------
+# cost tables of config 5's architecture (32 x 32 grid, n = 1024): the table
+# kernels against Architecture::createDistanceTable of the reference, which
+# runs in a host process of its own while the GPU arm works
+# ---------------------------------------------------------------------------
+def _tables_ref_worker(path):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "mqt-qmap_b200"))
+    from oracle import refapi
+    from qmap_b200 import architecture as ar
+    n, cm = ar.grid(32, 32)
+    R = refapi.Ref()
+    t0 = time.perf_counter()
+    ra = R.arch_create(n, sorted(cm))
+    dt = time.perf_counter() - t0
+    np.savez(path, dist=ra.distance_table(False), dist_rev=ra.distance_table(True), seconds=dt)
+
+
+def tables_start():
+    import multiprocessing as mp
+    import tempfile
+    path = os.path.join(tempfile.mkdtemp(prefix="qmap_tables_"), "ref.npz")
+    p = mp.get_context("spawn").Process(target=_tables_ref_worker, args=(path,))
+    p.start()
+    return p, path
+
+
+def tables_finish(handle, device):
+    from qmap_b200 import architecture as ar
+    p, path = handle
+    n, cm = ar.grid(32, 32)
+    t0 = time.perf_counter()
+    a = ar.Architecture(n, cm, device=device)
+    info = a.info()
+    wall = time.perf_counter() - t0
+    d, dr = a.distance_table(False), a.distance_table(True)
+    log("tables: waiting for the reference's createDistanceTable (n = 1024)")
+    p.join(timeout=600)
+    out = {"architecture": "32 x 32 grid (n = 1024, 3968 coupling entries)",
+           "what": "Architecture::createDistanceTable: Dijkstra::buildTable + buildSingleEdgeSkipTable",
+           "gpu_kernel_ms": float(info.table_build_ms), "gpu_call_ms": 1e3 * wall,
+           "cpu_ms": None, "parity": None}
+    if p.exitcode == 0 and os.path.exists(path):
+        r = np.load(path)
+        out["cpu_ms"] = 1e3 * float(r["seconds"])
+        out["cpu"] = "the reference's sources (oracle/_ref), 1 core, beside the GPU arm"
+        out["parity"] = bool(np.array_equal(r["dist"], d) and np.array_equal(r["dist_rev"], dr))
+        out["speedup_kernel"] = out["cpu_ms"] / out["gpu_kernel_ms"]
+    else:
+        p.kill()
+    return out
+
+
 def _traffic(key):
     """Measured per-launch figures of the routing kernel from the committed ncu
     capture (profiles/traffic.json): DRAM bytes, L2 bytes, L2 peak."""
@@ -782,6 +835,9 @@ def main():
     if world == 1 and not args.no_extra:
         extras = [WORKLOADS[k](args) for k in ("c2", "c3", "c4") if k != wl.key]
     cpu = {}
+    tables = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.no_extra:
+        tables = tables_start()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # before CUDA is initialised in this process (workers are spawned)
         for w in [wl] + extras:
@@ -820,6 +876,12 @@ def main():
             ok = ok and o["parity"]["ok"]
         except Exception as e:  # noqa: BLE001
             out[name] = {"error": repr(e)}
+    if out is not None and tables is not None:
+        try:
+            out["tables"] = tables_finish(tables, local_rank)
+            ok = ok and out["tables"]["parity"] is not False
+        except Exception as e:  # noqa: BLE001
+            out["tables"] = {"error": repr(e)}
     if out is not None:
         emit(out)
     if world > 1:

@@ -74,6 +74,18 @@ def ref() -> refapi.Ref:
     return _ref
 
 
+_ref_archs = {}
+
+
+def ref_arch_cached(n, cm):
+    """parity.ref().arch_create, kept per process (the reference needs about a
+    minute for the tables of a 32 x 32 grid)."""
+    key = (n, tuple(sorted(cm)))
+    if key not in _ref_archs:
+        _ref_archs[key] = ref().arch_create(n, sorted(cm))
+    return _ref_archs[key]
+
+
 def have_ref() -> bool:
     return os.path.exists(refapi.REF_LIB)
 

@@ -102,7 +102,7 @@ def test_batch_of_relabelled_instances_matches_single_runs():
 
 def _run_generated(n, cm, circ, **kw):
     a = ar.Architecture(n, cm)
-    ra = parity.ref().arch_create(n, sorted(cm))
+    ra = parity.ref_arch_cached(n, cm)
     be = routing.CudaBackend(_abi.load(), a.handle)
     msg, out, rr = parity.run_pair(be, _abi.load(), ra, circ, **kw)
     return msg, out, rr
@@ -164,3 +164,18 @@ def test_reference_fidelity_known_answers(k):
         backend_for.keep = a
         return routing.CudaBackend(_abi.load(), a.handle), _abi.load()
     parity.check_fidelity_known_answer(k, backend_for)
+
+
+def test_grid_32x32_first_layers_of_config5():
+    """config 5's architecture (n = 1024) and circuit (100k CX on uniformly
+    random pairs, seed 5), defaults (dynamic layout, lookahead): its first 140
+    gates (38 SWAPs; a little further on the reference's search explodes),
+    call by call against the reference.  (The hash-distributed search over
+    several GPUs that BASELINE.json names for this config is not built; this
+    pins tables, placement and search at n = 1024 on one GPU.)"""
+    n, cm = ar.grid(32, 32)
+    full = qcirc.random_circuit(1024, 100000, 5)
+    circ = qcirc.Circuit(1024, ops=list(full.ops[:140]))
+    msg, out, rr = _run_generated(n, cm, circ)
+    assert msg == "", msg
+    assert rr.n_layers == 140 and rr.swaps == 38

@@ -178,7 +178,7 @@ def test_architecture_distance_tables_grid_32x32():
     """config 5's architecture (n = 1024); the reference needs about a minute."""
     n, cm = ar.grid(32, 32)
     a = ar.Architecture(n, cm)
-    ra = parity.ref().arch_create(n, sorted(cm))
+    ra = parity.ref_arch_cached(n, cm)
     assert np.array_equal(a.distance_table(False), ra.distance_table(False))
     assert np.array_equal(a.distance_table(True), ra.distance_table(True))
 
