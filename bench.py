@@ -72,7 +72,10 @@ def mapper_view(c, t, n_physical: int):
     stripped - operand q becomes its rank among the used qubits (Mapper.cpp:
     44-53, 166-172) - and InitialLayout::Identity places logical i on physical
     i for every original used index i (HeuristicMapper.cpp:176-183)."""
-    used = np.unique(np.concatenate([t, c[c >= 0]])) if len(t) else np.zeros(0, np.int32)
+    present = np.zeros(int(max(t.max(), c.max())) + 1 if len(t) else 1, dtype=bool)
+    present[t] = True
+    present[c[c >= 0]] = True
+    used = np.nonzero(present)[0].astype(np.int32)
     lut = np.full(int(used.max()) + 1 if len(used) else 1, -1, dtype=np.int32)
     lut[used] = np.arange(len(used), dtype=np.int32)
     t2 = lut[t].astype(np.int32)
@@ -283,7 +286,12 @@ class WorkloadC3(Workload):
         super().__init__(args)
         from qmap_b200 import workloads
         self.dir = workloads.c3_directory(ROOT)
-        k = len(workloads.c3_suite(self.dir))
+        k = len(workloads.c3_arrays(self.dir))
+        self.full = k > 100
+        if self.full:
+            # BASELINE.md section 3.3 at its stated size: every circuit x 64
+            # seeded placements x {forward only, + 1 bidirectional pass}
+            self.default_batch = k * 64 * 2
         self.name = (f"examples/*.qasm suite ({k} circuits, {os.path.relpath(self.dir, ROOT)}) on heavy-hex 27, "
                      "default heuristic + lookahead, circuits x seeded placements x "
                      "{forward, +1 bidirectional pass}")
@@ -293,16 +301,15 @@ class WorkloadC3(Workload):
         return dict(workloads.C3_CONFIG)
 
     def cpu_sample(self, cores):
-        return self.args.cpu_sample or 1000 * cores
+        # (the full suite holds circuits of 10^5 gates: whole rounds over it)
+        return self.args.cpu_sample or (151 * 8 if self.full else 1000 * cores)
 
     def ref_step_sample(self, cores):
-        return self.args.cpu_sample or 200 * cores
+        return self.args.cpu_sample or (151 * 4 if self.full else 200 * cores)
 
     def instance_gates(self, seed):
         from qmap_b200 import workloads
-        _, circ, passes = workloads.c3_instance_passes(self.dir, seed)
-        c, t = circ.gate_arrays()
-        return circ.n_qubits, c, t, passes
+        return workloads.c3_instance_arrays(self.dir, seed)
 
     def ref_architecture(self, R):
         from qmap_b200 import architecture as ar

@@ -80,6 +80,54 @@ def c3_instance_passes(circuit_dir: str, seed: int, n_physical: int = 27):
     return f, circ, c3_passes(circuit_dir, seed)
 
 
+_c3_arrays = {}
+
+
+def c3_arrays(circuit_dir: str):
+    """[(file name, n_qubits, control, target)] of the suite as gate arrays,
+    sorted by file name; parsed once and kept in <dir>/_gate_arrays.npz (the
+    full suite is 2 M gates: 13 s of parsing)."""
+    if circuit_dir in _c3_arrays:
+        return _c3_arrays[circuit_dir]
+    files = sorted(f for f in os.listdir(circuit_dir) if f.endswith(".qasm"))
+    cache = os.path.join(circuit_dir, "_gate_arrays.npz")
+    out = None
+    if os.path.exists(cache):
+        try:
+            z = np.load(cache)
+            if list(z["files"]) == files:
+                off = z["offsets"]
+                out = [(f, int(z["n_qubits"][i]), z["control"][off[i]:off[i + 1]], z["target"][off[i]:off[i + 1]])
+                       for i, f in enumerate(files)]
+        except Exception:  # noqa: BLE001 (a stale or broken cache is rebuilt)
+            out = None
+    if out is None:
+        out = []
+        for f in files:
+            circ = qcirc.load_qasm(os.path.join(circuit_dir, f))
+            c, t = circ.gate_arrays()
+            out.append((f, circ.n_qubits, c, t))
+        try:
+            off = np.concatenate(([0], np.cumsum([len(x[2]) for x in out]))).astype(np.int64)
+            np.savez(cache, files=np.array(files), n_qubits=np.array([x[1] for x in out]), offsets=off,
+                     control=np.concatenate([x[2] for x in out]), target=np.concatenate([x[3] for x in out]))
+        except OSError:
+            pass
+    _c3_arrays[circuit_dir] = out
+    return out
+
+
+def c3_instance_arrays(circuit_dir: str, seed: int, n_physical: int = 27):
+    """c3_instance_passes as gate arrays: (n_physical, control, target, passes);
+    equal to c3_instance(...)[1].gate_arrays() without building Op lists."""
+    suite = c3_arrays(circuit_dir)
+    f, nq, c, t = suite[seed % len(suite)]
+    rng = np.random.default_rng([seed, len(f), nq])
+    perm = rng.permutation(n_physical).astype(np.int32)
+    c2 = np.where(c >= 0, perm[np.maximum(c, 0)], -1).astype(np.int32)
+    return n_physical, c2, perm[t].astype(np.int32), (seed // len(suite)) % 2
+
+
 def c3_directory(root: str) -> str:
     """The circuit suite of config 3: all of the reference's examples/*.qasm
     where tools/fetch_examples.py has copied them (tests/golden/circuits_full,
