@@ -2989,7 +2989,9 @@ template <int H, bool kFull> struct Search {
     const uint32_t placeBefore = nPlace;
     record = finalPass;
     if (!mapUnmappedGates()) {
-      return ST_BAD_ARG;
+      // no free physical qubit (pair) within reach: the reference's search
+      // then runs dry ("No viable mapping found.", :637-639)
+      return ST_NO_VIABLE;
     }
     LayerStats st;
     int rc;
@@ -3027,7 +3029,7 @@ template <int H, bool kFull> struct Search {
       }
       setLayer(l);
       if (!mapUnmappedGates()) {
-        return ST_BAD_ARG;
+        return ST_NO_VIABLE;
       }
       resume = true;
     }
