@@ -227,7 +227,7 @@ class WorkloadC4(Workload):
     circuit not at all."""
     key = "c4"
     n = 127
-    default_batch = 16384
+    default_batch = 32768
 
     def __init__(self, args):
         super().__init__(args)
@@ -874,7 +874,7 @@ def main():
         name = {"c2": "config2", "c3": "config3", "c4": "config4"}[w.key]
         try:
             Bx = w.default_batch
-            o = b200_arm(args, w, Bx, min(args.steps, 3), 3, rank, world, local_rank,
+            o = b200_arm(args, w, Bx, min(args.steps, 2), 3, rank, world, local_rank,
                          config_of(w, Bx), cpu.get(w.key))
             keep = ("value", "unit", "steps", "warmup", "ms_per_step", "config", "clocks", "e2e", "e2e_full",
                     "gpu_launches", "roofline", "roofline_l2", "parity", "cpu_baseline", "circuits_per_s",

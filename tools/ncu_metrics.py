@@ -25,7 +25,10 @@ WANT = ['gpu__time_duration.sum', 'launch__registers_per_thread', 'launch__grid_
         'smsp__sass_inst_executed_op_local_ld.sum', 'smsp__sass_inst_executed_op_local_st.sum',
         'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'sm__cycles_elapsed.max',
         'sm__icc_requests_lookup_hit.sum', 'sm__icc_requests_lookup_miss.sum',
-        'gcc__icc_requests.sum']
+        'gcc__cache_requests_type_instruction.sum',
+        'gcc__cache_requests_type_instruction.sum.pct_of_peak_sustained_elapsed',
+        'sm__icc_request_hit_rate.pct', 'sm__icc_requests.sum',
+        'lts__t_sectors.avg.pct_of_peak_sustained_elapsed']
 
 
 def main():
