@@ -784,6 +784,19 @@ def b200_arm(args, wl, B, steps, warmup, rank, world, local_rank, config, cpu):
                               "l2_hit_pct": tr.get("l2_hit_pct"),
                               "issue_slot_busy_pct": tr.get("issue_slot_busy_pct"),
                               "source": tr.get("source")}
+    if tr.get("gpc_icache_requests_per_expanded_node") and tr.get("gpc_icache_requests_pct_of_peak"):
+        # what actually bounds the kernel: the request
+        # rate of the GPC-level instruction cache.  Requests per expanded node
+        # and the peak rate (requests/s at 100 %) come from the ncu capture;
+        # the achieved rate is this run's.
+        peak_rps = tr["gpc_icache_requests"] / tr["kernel_s_under_ncu"] / (tr["gpc_icache_requests_pct_of_peak"] / 100)
+        ach = tr["gpc_icache_requests_per_expanded_node"] * exp / avg_launch_s
+        out["roofline_ifetch"] = {"bound": "gpc instruction cache request rate", "achieved": ach / 1e9,
+                                  "peak": peak_rps / 1e9, "unit": "G requests/s", "frac": ach / peak_rps,
+                                  "requests_per_expanded_node": tr["gpc_icache_requests_per_expanded_node"],
+                                  "sm_icache_hit_pct": tr.get("sm_icache_hit_pct"),
+                                  "warp_instructions_per_expanded_node": tr.get("warp_instructions_per_expanded_node"),
+                                  "source": tr.get("source")}
     return out
 
 
@@ -877,7 +890,7 @@ def main():
             o = b200_arm(args, w, Bx, min(args.steps, 2), 3, rank, world, local_rank,
                          config_of(w, Bx), cpu.get(w.key))
             keep = ("value", "unit", "steps", "warmup", "ms_per_step", "config", "clocks", "e2e", "e2e_full",
-                    "gpu_launches", "roofline", "roofline_l2", "parity", "cpu_baseline", "circuits_per_s",
+                    "gpu_launches", "roofline", "roofline_l2", "roofline_ifetch", "parity", "cpu_baseline", "circuits_per_s",
                     "expanded_nodes_per_step", "generated_nodes_per_step", "grid", "block")
             out[name] = {k: o[k] for k in keep if k in o}
             ok = ok and o["parity"]["ok"]

@@ -448,5 +448,78 @@ class Architecture:
             return 0.0
         return float(t[skip_edges, a, b])
 
+    # ---- utilities next to the tables (host only, used by the
+    # reference's exact mapper, nothing on the heuristic path calls them)
+    def minimum_number_of_swaps(self, permutation, limit: int = -1) -> int:
+        """Architecture::minimumNumberOfSwaps(permutation, limit)
+        (src/sc/Architecture.cpp:296-385): the fewest SWAPs on coupling edges
+        among the qubits of `permutation` that take the identity to the goal
+        "sorted(permutation)[k] holds permutation[k]"; with a limit, limit + 1
+        as soon as no solution below it exists.  Breadth-first over layouts
+        with a visited set (the reference's uniform-cost search without one
+        returns the same count)."""
+        perm = [int(q) for q in permutation]
+        qubits = sorted(set(perm))
+        goal = {q: perm[k] for k, q in enumerate(qubits)}
+        if all(q == g for q, g in goal.items()):
+            return 0
+        qs = set(qubits)
+        cm = self._cm_set()
+        swaps = set()
+        for a, b in self.coupling_map:
+            if a in qs and b in qs and (not self.bidirectional() or ((a, b) not in swaps and (b, a) not in swaps)):
+                swaps.add((a, b))
+        swaps = sorted(swaps)
+        start = tuple(range(self.n_qubits))
+        frontier = [start]
+        seen = {start}
+        depth = 0
+        while frontier:
+            if limit != -1 and depth >= limit:
+                return limit + 1
+            nxt = []
+            for cur in frontier:
+                for a, b in swaps:
+                    lst = list(cur)
+                    lst[a], lst[b] = lst[b], lst[a]
+                    if all(lst[q] == g for q, g in goal.items()):
+                        return depth + 1
+                    t = tuple(lst)
+                    if t not in seen:
+                        seen.add(t)
+                        nxt.append(t)
+            frontier = nxt
+            depth += 1
+        return 0
+
+    def get_coupling_limit(self, qubit_choice=None) -> int:
+        """Architecture::getCouplingLimit() / getCouplingLimit(qubitChoice)
+        (src/sc/Architecture.cpp:480-569): the longest of the shortest paths in
+        the undirected coupling graph (induced on qubit_choice): the
+        reference's exhaustive walk over simple paths keeps the smallest step
+        count per qubit, i.e. its breadth-first distance."""
+        choice = None if qubit_choice is None else set(int(q) for q in qubit_choice)
+        adj = [set() for _ in range(self.n_qubits)]
+        for a, b in self.coupling_map:
+            if choice is None or (a in choice and b in choice):
+                adj[a].add(b)
+                adj[b].add(a)
+        best = 0
+        for s0 in range(self.n_qubits):
+            if choice is not None and not adj[s0]:
+                continue
+            dist = {s0: 0}
+            frontier = [s0]
+            while frontier:
+                nxt = []
+                for u in frontier:
+                    for v in adj[u]:
+                        if v not in dist:
+                            dist[v] = dist[u] + 1
+                            nxt.append(v)
+                frontier = nxt
+            best = max(best, max(dist.values()))
+        return best
+
     def to_arch_text(self) -> str:
         return f"{self.n_qubits}\n" + "\n".join(f"{a} {b}" for a, b in self.coupling_map) + "\n"

@@ -323,6 +323,27 @@ int qref_arch_set_error_rates(void* h, const double* q1err,
   QREF_CATCH(1)
 }
 void qref_arch_destroy(void* h) { delete static_cast<RefArch*>(h); }
+// Architecture::minimumNumberOfSwaps(permutation, limit) (Architecture.cpp:296-385)
+long long qref_arch_minimum_number_of_swaps(void* h, const std::uint16_t* perm,
+                                            std::size_t n, long long limit) {
+  QREF_TRY
+  auto* a = static_cast<RefArch*>(h);
+  std::vector<std::uint16_t> p(perm, perm + n);
+  return static_cast<long long>(a->arch.minimumNumberOfSwaps(p, limit));
+  QREF_CATCH(-2)
+}
+// Architecture::getCouplingLimit() / (qubitChoice) (Architecture.cpp:480-569)
+long long qref_arch_coupling_limit(void* h, const std::uint16_t* choice,
+                                   std::size_t nChoice) {
+  QREF_TRY
+  auto* a = static_cast<RefArch*>(h);
+  if (choice == nullptr) {
+    return static_cast<long long>(a->arch.getCouplingLimit());
+  }
+  const std::set<std::uint16_t> c(choice, choice + nChoice);
+  return static_cast<long long>(a->arch.getCouplingLimit(c));
+  QREF_CATCH(-2)
+}
 int qref_arch_info(void* h, qmg_arch_info* info) {
   auto* a = static_cast<RefArch*>(h);
   std::memset(info, 0, sizeof(*info));

@@ -413,6 +413,25 @@ class RefArch:
             raise RuntimeError(self.ref._err())
         self.refresh()
 
+    def minimum_number_of_swaps(self, permutation, limit=-1) -> int:
+        L = self.ref.lib
+        L.qref_arch_minimum_number_of_swaps.restype = C.c_longlong
+        L.qref_arch_minimum_number_of_swaps.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_longlong]
+        p = np.ascontiguousarray(permutation, dtype=np.uint16)
+        r = L.qref_arch_minimum_number_of_swaps(self.h, p.ctypes.data, len(p), int(limit))
+        if r == -2:
+            raise RuntimeError(self.ref._err())
+        return int(r)
+
+    def coupling_limit(self, qubit_choice=None) -> int:
+        L = self.ref.lib
+        L.qref_arch_coupling_limit.restype = C.c_longlong
+        L.qref_arch_coupling_limit.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        if qubit_choice is None:
+            return int(L.qref_arch_coupling_limit(self.h, None, 0))
+        c = np.ascontiguousarray(sorted(qubit_choice), dtype=np.uint16)
+        return int(L.qref_arch_coupling_limit(self.h, c.ctypes.data, len(c)))
+
     def distance_table(self, include_reversal_cost=True) -> np.ndarray:
         out = np.empty((self.n, self.n), dtype=np.float64)
         if self.ref.lib.qref_arch_distance_table(self.h, int(include_reversal_cost), out.ctypes.data):

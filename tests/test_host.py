@@ -258,3 +258,50 @@ def test_circuit_batch_rejects_bad_operands():
         routing.CircuitBatch.from_gate_lists(L, 4, [(np.array([0]), np.array([4]))], 0)
     with pytest.raises(_abi.QmapError):
         routing.CircuitBatch.from_gate_lists(L, 4, [(np.array([0]), np.array([1]))], 2)
+
+
+def test_minimum_number_of_swaps_and_coupling_limit_match_the_reference():
+    """SURVEY 8 f4: Architecture::minimumNumberOfSwaps (Architecture.cpp:296-385)
+    and getCouplingLimit (:480-569), host utilities, against the compiled
+    reference on the .arch fixtures and random permutations / subsets."""
+    rng = np.random.default_rng(4)
+    for name in ("ibm_qx4.arch", "ibmq_london.arch", "ibmq_yorktown.arch", "ibmq_bogota.arch",
+                 "ibmq_casablanca.arch"):
+        path = os.path.join(parity.ARCHS, name)
+        a = ar.Architecture().load_coupling_map(path)
+        ra = parity.ref().arch_load(path)
+        n = a.n_qubits
+        assert a.get_coupling_limit() == ra.coupling_limit(), name
+        for _ in range(12):
+            k = int(rng.integers(2, n + 1))
+            subset = sorted(int(x) for x in rng.choice(n, size=k, replace=False))
+            assert a.get_coupling_limit(subset) == ra.coupling_limit(subset), (name, subset)
+            perm = [subset[i] for i in rng.permutation(k)]
+            # (the reference's search only ends when the goal can be reached:
+            # compare where the chosen qubits are connected among themselves)
+            if a.get_coupling_limit(subset) > 0 and _connected(a, subset):
+                want = ra.minimum_number_of_swaps(perm)
+                assert a.minimum_number_of_swaps(perm) == want, (name, perm)
+                if want > 1:
+                    assert a.minimum_number_of_swaps(perm, want - 1) == ra.minimum_number_of_swaps(perm, want - 1)
+    for n_, cm in (ar.heavy_hex_27(), ar.grid(4, 5), ar.line(9)):
+        a = ar.Architecture(n_, cm)
+        ra = parity.ref().arch_create(n_, sorted(cm))
+        assert a.get_coupling_limit() == ra.coupling_limit()
+
+
+def _connected(a, subset):
+    s = set(subset)
+    adj = {q: set() for q in s}
+    for x, y in a.coupling_map:
+        if x in s and y in s:
+            adj[x].add(y)
+            adj[y].add(x)
+    seen, todo = {subset[0]}, [subset[0]]
+    while todo:
+        u = todo.pop()
+        for v in adj[u]:
+            if v not in seen:
+                seen.add(v)
+                todo.append(v)
+    return seen == s
