@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32,
                  SearchMem* __restrict__ mem, uint32_t* __restrict__ ticket,
                  Scratch lay, uint32_t startFull) {
   extern __shared__ __align__(16) uint8_t smem[];
-  const int warp = static_cast<int>(threadIdx.x) >> 5;
+  const int warp = kWarpsPerCta == 1 ? 0 : static_cast<int>(threadIdx.x) >> 5;
   const int lane = static_cast<int>(threadIdx.x) & 31;
   const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
   Scratch S = lay;

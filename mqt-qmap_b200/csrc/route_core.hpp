@@ -25,10 +25,12 @@
 #define QMG_HD __host__ __device__ __forceinline__
 #define QMG_D __device__ __forceinline__
 #define QMG_NOUNROLL _Pragma("unroll 1")
+#define QMG_PRAGMA_(x) _Pragma(#x)
+#define QMG_UNROLL(n) QMG_PRAGMA_(unroll n)
 // (measured: out-of-line reductions cost 6 % on config 2, so the default is
 // inline; -DQMG_OUTLINE_REDUCTIONS keeps the experiment buildable)
 #if defined(QMG_OUTLINE_REDUCTIONS)
-#define QMG_HD_RED __host__ __device__ __noinline__
+#define QMG_HD_RED inline __host__ __device__ __noinline__
 #else
 #define QMG_HD_RED QMG_HD
 #endif
@@ -39,6 +41,7 @@
 #define QMG_HD inline
 #define QMG_D inline
 #define QMG_NOUNROLL
+#define QMG_UNROLL(n)
 #endif
 
 namespace qmg {
@@ -61,8 +64,32 @@ constexpr uint32_t kScanMax = QMG_SCAN_MAX;
 // open lists longer than kBlkMin keep the top of every kBlk-entry block, so
 // that a pop reads the block tops and re-scans one block instead of the list
 #ifndef QMG_BLK
-#define QMG_BLK 512
+#define QMG_BLK 256
+#endif
+#ifndef QMG_BLK_MIN
 #define QMG_BLK_MIN 4096
+#endif
+// The kernel is bound by instruction fetch, so the
+// unrolling / in-flight factors below are kept as small as the latency they
+// hide allows.  Measured on config 4, 32768 instances per step (M expanded
+// nodes/s): 65.4 with (block 512, flight 4, scans 4/3, wide 4, two inlined
+// commit paths in push) -> 75.8 (one commit path, block 256, flight 2) -> 79.4
+// (scans 2/1) -> 82.4 (global-address hint, glob()) -> 83.5 (wide 2).
+// unrolling of the fidelity heuristic's scans over physical qubits (1q gates)
+// and coupling edges (2q gates; only run when the memo misses)
+#ifndef QMG_SCAN1_UNROLL
+#define QMG_SCAN1_UNROLL 2
+#endif
+#ifndef QMG_SCAN2_UNROLL
+#define QMG_SCAN2_UNROLL 1
+#endif
+// open-list entries in flight per lane when block tops / blocks are scanned
+#ifndef QMG_WIDE
+#define QMG_WIDE 2
+#endif
+// layout comparisons in flight per lane in pushChunk's look-up
+#ifndef QMG_FLIGHT
+#define QMG_FLIGHT 2
 #endif
 constexpr uint32_t kPairGates = 2;
 constexpr uint32_t kBlk = QMG_BLK;  // (tests build the host variant with 4 / 8)
@@ -463,6 +490,15 @@ template <class T> QMG_HD T ldg(const T* p) {
 // circuit tables are read with plain (coherent) loads: they may be the
 // search's private copy, which the search rewrites when it splits a layer
 template <class T> QMG_HD T ldc(const T* p) { return *p; }
+// node pools, open lists and tables are reached through pointers kept in
+// shared memory, which the compiler must treat as generic addresses; they
+// always point into the launch's arenas in global memory
+template <class T> QMG_HD T* glob(T* p) {
+#if defined(__CUDA_ARCH__) && !defined(QMG_NO_GLOBAL_HINT)
+  __builtin_assume(__isGlobal(p));
+#endif
+  return p;
+}
 QMG_HD Gate2 ldGate(const Gate2* p) {
 #if defined(__CUDA_ARCH__)
   const uint2 v = *reinterpret_cast<const uint2*>(p);
@@ -903,12 +939,12 @@ template <int H, bool kFull> struct Search {
   }
 
   QMG_HD NodeHdr* hdr(uint32_t idx) const {
-    return reinterpret_cast<NodeHdr*>(M.pool +
+    return reinterpret_cast<NodeHdr*>(glob(M.pool) +
                                       static_cast<size_t>(idx) * M.recBytes);
   }
   QMG_HD int16_t* nodeQ(uint32_t idx) const {
     return reinterpret_cast<int16_t*>(
-        M.pool + static_cast<size_t>(idx) * M.recBytes + sizeof(NodeHdr));
+        glob(M.pool) + static_cast<size_t>(idx) * M.recBytes + sizeof(NodeHdr));
   }
   QMG_HD int16_t* nodeL(uint32_t idx) const { return nodeQ(idx) + padN(n); }
   QMG_HD bool considered(int q) const {
@@ -1378,9 +1414,7 @@ template <int H, bool kFull> struct Search {
           const int sLoc = g.bcast(loc, src);
           const double sCurr = g.bcast(curr, src);
           double v = 0.;
-#if defined(__CUDA_ARCH__)
-#pragma unroll 4
-#endif
+          QMG_UNROLL(QMG_SCAN1_UNROLL)
           for (int p = g.lane; p < n; p += Group::W) {
             const double cp = ldg(A.c1 + p);
             if (cp >= sCurr) {
@@ -1415,7 +1449,7 @@ template <int H, bool kFull> struct Search {
         const uint64_t key = pairKey();
         if (memo && act) {
           slot = (static_cast<size_t>(i) * n + l1) * n + l2;
-          const PairSlot ps = M.pair[slot];
+          const PairSlot ps = glob(M.pair)[slot];
           if (ps.tag == key) {
             sc = ps.val;
             hit = true;
@@ -1430,9 +1464,7 @@ template <int H, bool kFull> struct Search {
           const int s2 = g.bcast(l2, src);
           double v = DBL_MAX;
           // (iterations are independent gathers: unrolled so that they overlap)
-#if defined(__CUDA_ARCH__)
-#pragma unroll 3
-#endif
+          QMG_UNROLL(QMG_SCAN2_UNROLL)
           for (int k = g.lane; k < A.nE; k += Group::W) {
             const int q3 = ldg(A.edges + 2 * k);
             const int q4 = ldg(A.edges + 2 * k + 1);
@@ -1452,7 +1484,7 @@ template <int H, bool kFull> struct Search {
               PairSlot ps;
               ps.tag = key;
               ps.val = v;
-              M.pair[slot] = ps;
+              glob(M.pair)[slot] = ps;
             }
           }
         }
@@ -1511,10 +1543,10 @@ template <int H, bool kFull> struct Search {
   QMG_HD OpenCtx octx() const { return OpenCtx{M.pool, M.recBytes, n}; }
   QMG_HD static const int16_t* nodeQOf(const OpenCtx& c, uint32_t idx) {
     return reinterpret_cast<const int16_t*>(
-        c.pool + static_cast<size_t>(idx) * c.recBytes + sizeof(NodeHdr));
+        glob(c.pool) + static_cast<size_t>(idx) * c.recBytes + sizeof(NodeHdr));
   }
   QMG_HD static const NodeHdr* hdrOf(const OpenCtx& c, uint32_t idx) {
-    return reinterpret_cast<const NodeHdr*>(c.pool +
+    return reinterpret_cast<const NodeHdr*>(glob(c.pool) +
                                             static_cast<size_t>(idx) * c.recBytes);
   }
   // 4 consecutive qubits[] entries as one integer whose unsigned order is the
@@ -1569,7 +1601,7 @@ template <int H, bool kFull> struct Search {
   // then narrowed key by key (cost band, validity, heuristic band, valid-gate
   // count, lexicographic layout), which selects the same node as the pairwise
   // order whenever that order is a strict weak order.
-  // kWide: four entries per lane are loaded before they are compared, so that
+  // kWide: QMG_WIDE entries per lane are loaded before they are compared, so that
   // their memory latencies overlap (long lists: the entries come from L2/HBM)
   template <bool kWide = false>
   QMG_HD static uint32_t topOfS(const OpenCtx& c, const OpenEntry* arr,
@@ -1586,13 +1618,14 @@ template <int H, bool kFull> struct Search {
     best.valid = 0;
     uint32_t i = lo + g.lane;
     if (kWide) {
+      constexpr uint32_t kIn = QMG_WIDE;  // entries in flight per lane
       QMG_NOUNROLL
-      for (; i + 3 * Group::W < hi; i += 4 * Group::W) {
-        OpenEntry e[4];
-        for (int u = 0; u < 4; ++u) {
-          e[u] = arr[i + u * Group::W];
+      for (; i + (kIn - 1) * Group::W < hi; i += kIn * Group::W) {
+        OpenEntry e[kIn];
+        for (uint32_t u = 0; u < kIn; ++u) {
+          e[u] = glob(arr)[i + u * Group::W];
         }
-        for (int u = 0; u < 4; ++u) {
+        for (uint32_t u = 0; u < kIn; ++u) {
           if (bestPos == kNone || hasPriorityOf(c, e[u], best)) {
             best = e[u];
             bestPos = i + u * Group::W;
@@ -1602,7 +1635,7 @@ template <int H, bool kFull> struct Search {
     }
     QMG_NOUNROLL
     for (; i < hi; i += Group::W) {
-      const OpenEntry e = arr[i];
+      const OpenEntry e = glob(arr)[i];
       if (bestPos == kNone || hasPriorityOf(c, e, best)) {
         best = e;
         bestPos = i;
@@ -1652,9 +1685,9 @@ template <int H, bool kFull> struct Search {
     const uint32_t hi = lo + kBlk < nOpen ? lo + kBlk : nOpen;
     const uint32_t p = blkTopOf(c, open, lo, hi);
     if (g.lane == 0) {
-      OpenEntry e = open[p];
+      OpenEntry e = glob(open)[p];
       e.hash = p;  // (block tops carry their position, not the layout hash)
-      btop[b] = e;
+      glob(btop)[b] = e;
     }
     g.sync();
   }
@@ -1673,7 +1706,7 @@ template <int H, bool kFull> struct Search {
                                    uint32_t nOpen) {
     const uint32_t nb = (nOpen + kBlk - 1) / kBlk;
     const uint32_t b = blkTopOf(c, btop, 0, nb);
-    return btop[b];
+    return glob(btop)[b];
   }
   // the entry e at pos was appended (fresh: it opened a new block) or replaced
   // by a better one
@@ -1684,12 +1717,12 @@ template <int H, bool kFull> struct Search {
       const uint32_t b = pos / kBlk;
       bool take = fresh;
       if (!take) {
-        const OpenEntry t = btop[b];
+        const OpenEntry t = glob(btop)[b];
         take = t.idx == e.idx || hasPriorityOf(c, e, t);
       }
       if (take) {
         e.hash = pos;  // (block tops carry their position, not the hash)
-        btop[b] = e;
+        glob(btop)[b] = e;
       }
     }
     g.sync();
@@ -1718,7 +1751,7 @@ template <int H, bool kFull> struct Search {
       return e;
     }
     pos = topOfS(octx(), M.open, 0, nOpen);
-    return M.open[pos];
+    return glob(M.open)[pos];
   }
 
   // pop: take the entry at pos (node idx, goal flag valid) off the open list
@@ -1727,10 +1760,10 @@ template <int H, bool kFull> struct Search {
     const uint32_t last = nOpen - 1;
     uint32_t moved = kNone;
     if (pos != last) {
-      const OpenEntry e = M.open[last];
+      const OpenEntry e = glob(M.open)[last];
       moved = e.idx;
       if (g.lane == 0) {
-        M.open[pos] = e;
+        glob(M.open)[pos] = e;
         hdr(e.idx)->openPos = pos;
       }
     }
@@ -1910,13 +1943,13 @@ template <int H, bool kFull> struct Search {
       const uint32_t cur = curStamp();
       QMG_NOUNROLL
       for (uint32_t i = 0; i < nOpen; ++i) {
-        const OpenEntry e = M.open[i];
+        const OpenEntry e = glob(M.open)[i];
         uint32_t slot = homeSlot(e.hash);
         QMG_NOUNROLL
-        while (tabStamp(M.table[slot]) == cur) {
+        while (tabStamp(glob(M.table)[slot]) == cur) {
           slot = (slot + 1) & M.tableMask;
         }
-        M.table[slot] = tabPack(cur, e.hash, e.idx);
+        glob(M.table)[slot] = tabPack(cur, e.hash, e.idx);
       }
     }
     tableMode = true;
@@ -1974,12 +2007,12 @@ template <int H, bool kFull> struct Search {
       QMG_NOUNROLL
       for (uint32_t i0 = 0; i0 < nOpen && found == kNone; i0 += Group::W) {
         const uint32_t i = i0 + g.lane;
-        uint32_t m = g.ballot(i < nOpen && M.open[i].hash == h);
+        uint32_t m = g.ballot(i < nOpen && glob(M.open)[i].hash == h);
         QMG_NOUNROLL
         while (m != 0 && found == kNone) {
           const int src = ctz32(m);
           m &= m - 1;
-          const uint32_t idx = M.open[i0 + src].idx;
+          const uint32_t idx = glob(M.open)[i0 + src].idx;
           if (sameLayout(idx, ch, root)) {
             found = idx;
           }
@@ -1989,7 +2022,7 @@ template <int H, bool kFull> struct Search {
       const uint32_t cur = curStamp();
       slot = homeSlot(h);
       for (;;) {
-        const uint64_t e = M.table[slot];
+        const uint64_t e = glob(M.table)[slot];
         if (tabStamp(e) != cur) {
           break;  // free slot
         }
@@ -2004,42 +2037,41 @@ template <int H, bool kFull> struct Search {
         found = kNone;  // closed: the slot is re-pointed to the new node below
       }
     }
-    if (found != kNone) {
+    // one commit path for both outcomes (a second inlined copy of writeNode
+    // and blkChanged costs instruction-cache space, which is what bounds the
+    // kernel): either the record of the open duplicate is overwritten in
+    // place, or a new record, open entry and table entry are made
+    uint32_t idx = found;
+    uint32_t pos = 0;
+    const bool fresh = found == kNone;
+    if (!fresh) {
       // layout is in the open list: keep the better one (:63-79)
-      const uint32_t pos = hdr(found)->openPos;
-      const OpenEntry ex = M.open[pos];
-      const OpenEntry ne = entryOf(ch, found);
-      if (cmp4(ne, ex) < 0) {
-        // existing > new: replace in place (the old node was never expanded,
-        // so nothing refers to its record)
-        g.sync();
-        writeNode(found, ch, parentIdx, depth, id, pos, root);
-        if (g.lane == 0) {
-          M.open[pos] = ne;
-        }
-        g.sync();
-        if (kFull && blockMode) {
-          blkChanged(octx(), M.btop, ne, pos, false);
-        }
+      pos = hdr(found)->openPos;
+      const OpenEntry ex = glob(M.open)[pos];
+      if (!(cmp4(entryOf(ch, found), ex) < 0)) {
+        return true;
       }
-      return true;
+      // existing > new: replace in place (the old node was never expanded,
+      // so nothing refers to its record)
+      g.sync();
+    } else {
+      if (nPool >= M.poolCap) {
+        return false;
+      }
+      idx = nPool++;
+      pos = nOpen++;
     }
-    if (nPool >= M.poolCap) {
-      return false;
-    }
-    const uint32_t idx = nPool++;
-    const uint32_t pos = nOpen++;
     writeNode(idx, ch, parentIdx, depth, id, pos, root);
     const OpenEntry ne = entryOf(ch, idx);
     if (g.lane == 0) {
-      M.open[pos] = ne;
-      if (tableMode) {
-        M.table[slot] = tabPack(curStamp(), h, idx);
+      glob(M.open)[pos] = ne;
+      if (fresh && tableMode) {
+        glob(M.table)[slot] = tabPack(curStamp(), h, idx);
       }
     }
     g.sync();
     if (kFull && blockMode) {
-      blkChanged(octx(), M.btop, ne, pos, pos % kBlk == 0);
+      blkChanged(octx(), M.btop, ne, pos, fresh && pos % kBlk == 0);
     }
     return true;
   }
@@ -2077,7 +2109,7 @@ template <int H, bool kFull> struct Search {
         if (!done) {
           QMG_NOUNROLL
           for (;;) {
-            const uint64_t e = M.table[slot];
+            const uint64_t e = glob(M.table)[slot];
             if (tabStamp(e) != cur) {
               done = true;  // free slot: not in the table
               break;
@@ -2095,7 +2127,7 @@ template <int H, bool kFull> struct Search {
         }
         QMG_NOUNROLL
         while (m != 0) {
-          constexpr int kFlight = 4;
+          constexpr int kFlight = QMG_FLIGHT;
           int src[kFlight];
           bool diff[kFlight];
           for (int k = 0; k < kFlight; ++k) {
@@ -2185,42 +2217,37 @@ template <int H, bool kFull> struct Search {
           reprobe = true;  // it may have taken a free slot a later sibling holds
           continue;
         }
-        if (d == kReplace) {
-          const uint32_t fidx = g.bcast(found, j);
-          const uint32_t fpos = g.bcast(pos, j);
-          g.sync();
-          writeNode(fidx, ch, parentIdx, depth, id, fpos, false);
-          const OpenEntry ne = entryOf(ch, fidx);
-          if (g.lane == 0) {
-            M.open[fpos] = ne;
-          }
-          g.sync();
-          if (blockMode) {
-            blkChanged(octx(), M.btop, ne, fpos, false);
-          }
-          continue;
-        }
-        if (nPool >= M.poolCap) {
-          return false;
-        }
+        // (one commit path for kReplace and kNew, see pushOne)
+        const bool fresh = d != kReplace;
+        uint32_t idx = g.bcast(found, j);
+        uint32_t npos = g.bcast(pos, j);
         uint32_t sl = g.bcast(slot, j);
-        if (reprobe && g.bcast(freeSlot, j)) {
-          QMG_NOUNROLL
-          while (tabStamp(M.table[sl]) == cur) {
-            sl = (sl + 1) & M.tableMask;
+        if (!fresh) {
+          g.sync();
+        } else {
+          if (nPool >= M.poolCap) {
+            return false;
           }
+          if (reprobe && g.bcast(freeSlot, j)) {
+            QMG_NOUNROLL
+            while (tabStamp(glob(M.table)[sl]) == cur) {
+              sl = (sl + 1) & M.tableMask;
+            }
+          }
+          idx = nPool++;
+          npos = nOpen++;
         }
-        const uint32_t idx = nPool++;
-        const uint32_t npos = nOpen++;
         writeNode(idx, ch, parentIdx, depth, id, npos, false);
         const OpenEntry ne = entryOf(ch, idx);
         if (g.lane == 0) {
-          M.open[npos] = ne;
-          M.table[sl] = tabPack(cur, ch.hash, idx);
+          glob(M.open)[npos] = ne;
+          if (fresh) {
+            glob(M.table)[sl] = tabPack(cur, ch.hash, idx);
+          }
         }
         g.sync();
         if (blockMode) {
-          blkChanged(octx(), M.btop, ne, npos, npos % kBlk == 0);
+          blkChanged(octx(), M.btop, ne, npos, fresh && npos % kBlk == 0);
         }
       }
     }
@@ -2545,7 +2572,7 @@ template <int H, bool kFull> struct Search {
     if ((s & kStampMask) == 0) {
       QMG_NOUNROLL
       for (uint32_t i = g.lane; i <= M.tableMask; i += Group::W) {
-        M.table[i] = 0;
+        glob(M.table)[i] = 0;
       }
       ++s;
     }
@@ -2568,34 +2595,38 @@ template <int H, bool kFull> struct Search {
     }
     g.sync();
     int32_t got = -1;
-    if (g.lane == 0) {
-      uint32_t i = static_cast<uint32_t>(M.stamp * 2654435761U) % M.nBig;
-      for (;;) {
 #if defined(__CUDA_ARCH__)
-        if (atomicCAS(&M.big[i].lock, 0U, 1U) == 0U) {
-          got = static_cast<int32_t>(i);
-          break;
+    for (;;) {
+      if (g.lane == 0) {
+        const uint32_t i0 = static_cast<uint32_t>(M.stamp * 2654435761U) % M.nBig;
+        for (uint32_t k = 0; k < M.nBig; ++k) {
+          const uint32_t i = (i0 + k) % M.nBig;
+          if (atomicCAS(&M.big[i].lock, 0U, 1U) == 0U) {
+            got = static_cast<int32_t>(i);
+            break;
+          }
         }
-        i = (i + 1) % M.nBig;
-        if (i == 0) {
+        if (got < 0) {
           __nanosleep(2000);
+        } else {
+          __threadfence();
         }
-#else
-        if (M.big[i].lock == 0U) {
-          M.big[i].lock = 1U;
-          got = static_cast<int32_t>(i);
-          break;
-        }
-        i = (i + 1) % M.nBig;
-        if (i == 0) {
-          break;  // (single-threaded host build: nobody will release one)
-        }
-#endif
       }
-#if defined(__CUDA_ARCH__)
-      __threadfence();
-#endif
+      if (g.bcast(got, 0) >= 0) {
+        break;
+      }
     }
+#else
+    for (uint32_t k = 0; k < M.nBig; ++k) {
+      // (single-threaded host build: nobody will release one)
+      const uint32_t i = (static_cast<uint32_t>(M.stamp * 2654435761U) + k) % M.nBig;
+      if (M.big[i].lock == 0U) {
+        M.big[i].lock = 1U;
+        got = static_cast<int32_t>(i);
+        break;
+      }
+    }
+#endif
     got = g.bcast(got, 0);
     if (got < 0) {
       return false;
@@ -2645,7 +2676,7 @@ template <int H, bool kFull> struct Search {
     }
     QMG_NOUNROLL
     for (uint32_t i = g.lane; i < nOpen; i += Group::W) {
-      M.open[i] = M.open0[i];
+      glob(M.open)[i] = M.open0[i];
     }
     g.sync();
     newTableStamp();

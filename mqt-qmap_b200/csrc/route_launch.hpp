@@ -9,7 +9,10 @@
 
 namespace qmg {
 
-constexpr int kWarpsPerCta = 4;
+#ifndef QMG_WARPS_PER_CTA
+#define QMG_WARPS_PER_CTA 4
+#endif
+constexpr int kWarpsPerCta = QMG_WARPS_PER_CTA;
 #ifndef QMG_MIN_CTAS
 // 6 CTAs (24 warps, 80 registers/thread) per SM measured best on config 2:
 // 3/4/5/6/8 -> 102/153/166/172/166 M nodes/s (the grid still holds 8 CTAs per
