@@ -74,7 +74,8 @@ constexpr uint32_t kScanMax = QMG_SCAN_MAX;
 // hide allows.  Measured on config 4, 32768 instances per step (M expanded
 // nodes/s): 65.4 with (block 512, flight 4, scans 4/3, wide 4, two inlined
 // commit paths in push) -> 75.8 (one commit path, block 256, flight 2) -> 79.4
-// (scans 2/1) -> 82.4 (global-address hint, glob()) -> 83.5 (wide 2).
+// (scans 2/1) -> 82.4 (global-address hint, glob()) -> 83.5 (wide 2); at 16384
+// instances per step: 70.7 -> 75.3 (QMG_TABLE_FROM_START).
 // unrolling of the fidelity heuristic's scans over physical qubits (1q gates)
 // and coupling edges (2q gates; only run when the memo misses)
 #ifndef QMG_SCAN1_UNROLL
@@ -87,6 +88,13 @@ constexpr uint32_t kScanMax = QMG_SCAN_MAX;
 #ifndef QMG_WIDE
 #define QMG_WIDE 2
 #endif
+// the full search variant indexes the open list by the layout hash table from
+// the first node of a layer on (the lean variant scans open lists of up to
+// QMG_SCAN_MAX nodes): all children then take pushChunk, and pushOne with its
+// copies of the layout comparison and the record write leaves the hot code
+#ifndef QMG_TABLE_FROM_START
+#define QMG_TABLE_FROM_START 1
+#endif
 // layout comparisons in flight per lane in pushChunk's look-up
 #ifndef QMG_FLIGHT
 #define QMG_FLIGHT 2
@@ -94,6 +102,7 @@ constexpr uint32_t kScanMax = QMG_SCAN_MAX;
 constexpr uint32_t kPairGates = 2;
 constexpr uint32_t kBlk = QMG_BLK;  // (tests build the host variant with 4 / 8)
 constexpr uint32_t kBlkMin = QMG_BLK_MIN;
+constexpr bool kTableFromStart = QMG_TABLE_FROM_START != 0;
 
 enum Status : int32_t {
   ST_OK = 0,
@@ -2000,10 +2009,12 @@ template <int H, bool kFull> struct Search {
     const uint64_t h = ch.hash;
     uint32_t found = kNone;  // pool index of an OPEN node with this layout
     uint32_t slot = 0;
-    if (!tableMode && nOpen > kScanMax) {
+    // (kAlwaysTable: the scan below is not part of the full variant's code)
+    constexpr bool kAlwaysTable = kFull && kTableFromStart;
+    if (!kAlwaysTable && !tableMode && nOpen > kScanMax) {
       buildTable();
     }
-    if (!tableMode) {
+    if (!kAlwaysTable && !tableMode) {
       QMG_NOUNROLL
       for (uint32_t i0 = 0; i0 < nOpen && found == kNone; i0 += Group::W) {
         const uint32_t i = i0 + g.lane;
@@ -2717,7 +2728,7 @@ template <int H, bool kFull> struct Search {
     if (!resume) {
       nPool = 0;
       nOpen = 0;
-      tableMode = false;
+      tableMode = kFull && kTableFromStart;
       blockMode = false;
       if (g.lane == 0) {
         ++M.stamp;  // (M lives in shared memory on the device)
