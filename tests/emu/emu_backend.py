@@ -21,8 +21,12 @@ def build(asan: bool = False) -> str:
     # QMG_EMU_BLK="4,8": open-list blocks of 4 entries from 8 open nodes on, so
     # that the small golden cases exercise the blocked open list
     blk = os.environ.get("QMG_EMU_BLK", "")
-    out = os.path.join(HERE, "libqmg_emu_asan.so" if asan else
-                       (f"libqmg_emu_blk_{blk.replace(',', '_')}.so" if blk else "libqmg_emu.so"))
+    # QMG_EMU_DEFS="QMG_FLIGHT=4,QMG_WIDE=4": other settings of the kernel's
+    # tuning macros (they must not change any result)
+    defs = [d for d in os.environ.get("QMG_EMU_DEFS", "").split(",") if d]
+    tag = (("_blk_" + blk.replace(",", "_")) if blk else "") + \
+        (("_" + "_".join(d.replace("=", "") for d in defs)) if defs else "")
+    out = os.path.join(HERE, "libqmg_emu_asan.so" if asan else f"libqmg_emu{tag}.so")
     src = os.path.join(HERE, "emu.cpp")
     deps = [src] + [os.path.join(ROOT, "mqt-qmap_b200", "csrc", f)
                     for f in ("route_core.hpp", "layers.hpp", "host_api.hpp", "flatten.hpp",
@@ -39,6 +43,7 @@ def build(asan: bool = False) -> str:
         flags += [f"-DQMG_BLK={int(parts[0])}", f"-DQMG_BLK_MIN={int(parts[1])}"]
         if len(parts) > 2:
             flags += [f"-DQMG_SCAN_MAX={int(parts[2])}"]
+    flags += ["-D" + d for d in defs]
     subprocess.check_call([cxx, *flags, "-o", out, src])
     return out
 

@@ -140,7 +140,13 @@ def test_random_circuits_with_layer_splits_against_oracle(arch, calib):
                                  # large pool: the tiny private pool is for runs without splits)
                                  {"QMG_EMU_PRIVATE_POOL": "6", "QMG_EMU_BLK": "4,8,2"},
                                  {"QMG_EMU_PRIVATE_POOL": "40", "QMG_EMU_START_FULL": "1"},
-                                 {"QMG_EMU_START_FULL": "1"}])
+                                 {"QMG_EMU_START_FULL": "1"},
+                                 # other settings of the tuning macros: scan before the hash
+                                 # table, 4 comparisons / open entries in flight, unrolled scans
+                                 {"QMG_EMU_BLK": "4,8,2", "QMG_EMU_START_FULL": "1",
+                                  "QMG_EMU_DEFS": "QMG_TABLE_FROM_START=0,QMG_FLIGHT=4,QMG_WIDE=4"},
+                                 {"QMG_EMU_START_FULL": "1",
+                                  "QMG_EMU_DEFS": "QMG_FLIGHT=1,QMG_WIDE=1,QMG_SCAN1_UNROLL=4"}])
 def test_full_search_variant_matches_reference_outputs(env):
     """The kernel routes an instance with the lean search variant and again
     with the full one (per-block tops of the open list, layer splits) once an
