@@ -9,6 +9,9 @@
 // layout, routeCircuit's emission of SWAP / CX / H, gate counting, the result
 // JSON - stays the reference's code.
 //
+// Configuration::dataLoggingPath works as in the reference: the device's node
+// log is replayed through the reference's own DataLogger, layer by layer.
+//
 // What changes: the virtual aStarMap (HeuristicMapper.hpp:220) is answered
 // from ONE qmg_route_batch call that routes the whole circuit on the device
 // (all pseudo-routing passes, placements of mapUnmappedGates, every layer's
@@ -100,6 +103,9 @@ protected:
       b.effectiveBranchingFactor =
           computeEffectiveBranchingRate(b.expandedNodes + 1, r.solution_depth);
     }
+    if (results.config.dataLoggingEnabled()) {
+      logLayer(layer, node);
+    }
     return node;
   }
 
@@ -112,6 +118,54 @@ private:
   std::vector<qmg_layer_result> rec_;
   std::vector<std::int16_t> layerQ_;
   std::vector<std::uint16_t> swaps_;
+  // Configuration::dataLoggingPath: every node the device generated in the
+  // final pass (qmg_route_result.node_log) and every layer's root layout
+  std::vector<qmg_node_log_record> nodeLog_;
+  std::vector<std::int16_t> rootQ_;
+  std::size_t nodeLogPos_ = 0;
+
+  // what aStarMap writes through the DataLogger for one layer
+  // (HeuristicMapper.cpp:541-546, :741-747 logSearchNode for every generated
+  // node in generation order; :676-688 logFinalizeLayer), from the device's
+  // node log: a node's layout and SWAP list follow from its parent's
+  void logLayer(std::size_t layer, const Node& result) {
+    const auto n = architecture->getNqubits();
+    struct Made {
+      std::vector<std::int16_t> qubits;
+      std::vector<Exchange> swaps;
+    };
+    std::vector<Made> made;  // by node id (ids are dense per layer)
+    const std::vector<std::int16_t> root(
+        rootQ_.begin() + static_cast<std::ptrdiff_t>(layer * n),
+        rootQ_.begin() + static_cast<std::ptrdiff_t>((layer + 1) * n));
+    for (; nodeLogPos_ < nodeLog_.size() && nodeLog_[nodeLogPos_].layer == layer;
+         ++nodeLogPos_) {
+      const qmg_node_log_record& r = nodeLog_[nodeLogPos_];
+      Made m;
+      if (r.root != 0) {
+        m.qubits = root;
+      } else {
+        m = made.at(r.parent);
+        std::swap(m.qubits.at(r.swap_first), m.qubits.at(r.swap_second));
+        m.swaps.emplace_back(r.swap_first, r.swap_second, qc::SWAP);
+      }
+      dataLogger->logSearchNode(layer, r.id, r.parent, r.cost_fixed, r.cost_heur,
+                                r.lookahead_penalty, m.qubits, r.valid != 0, m.swaps,
+                                r.depth);
+      if (made.size() <= r.id) {
+        made.resize(static_cast<std::size_t>(r.id) + 1);
+      }
+      made[r.id] = std::move(m);
+    }
+    qc::CompoundOperation compOp{};
+    for (const auto& gate : layers.at(layer)) {
+      compOp.emplace_back(gate.op->clone());
+    }
+    dataLogger->logFinalizeLayer(layer, compOp, singleQubitMultiplicities.at(layer),
+                                 twoQubitMultiplicities.at(layer), root, result.id,
+                                 result.costFixed, result.costHeur, result.lookaheadPenalty,
+                                 result.qubits, result.swaps, result.depth);
+  }
 
   void release() {
     if (arch_ != nullptr) {
@@ -224,6 +278,8 @@ private:
     inst.layer_capacity = static_cast<std::uint32_t>(cap);
     const qmg_config cfg = deviceConfig();
     std::size_t swapCap = 16 * cap + 1024;
+    const bool logging = results.config.dataLoggingEnabled();
+    std::size_t logCap = logging ? (std::size_t{1} << 20) : 0;
     for (int attempt = 0;; ++attempt) {
       rec_.assign(cap, qmg_layer_result{});
       layerQ_.assign(cap * n, -1);
@@ -245,6 +301,13 @@ private:
       r.split_capacity = static_cast<std::uint32_t>(cap - nL);
       r.placement_log = placeLog.data();
       r.placement_log_capacity = n;
+      if (logging) {
+        nodeLog_.assign(logCap, qmg_node_log_record{});
+        rootQ_.assign(cap * n, -1);
+        r.node_log = nodeLog_.data();
+        r.node_log_capacity = static_cast<std::uint32_t>(logCap);
+        r.layer_root_qubits = rootQ_.data();
+      }
       qmg_route_stats st{};
       check(qmg_route_batch(arch_, &cfg, 1, &inst, &r, nullptr, &st));
       if (r.status == QMG_BUFFER_TOO_SMALL && attempt < 6) {
@@ -252,6 +315,20 @@ private:
         continue;
       }
       check(r.status);
+      if (logging) {
+        if (r.n_node_log > logCap && attempt < 6) {
+          logCap = r.n_node_log;  // (the log was cut: once more with room for it)
+          continue;
+        }
+        if (r.n_splits != 0) {
+          // (node ids restart when the device splits a layer; the reference
+          // writes one more file set per split, DataLogger::splitLayer)
+          throw QMAPException("qmap_b200: data logging of runs with automatic "
+                              "layer splits is not supported");
+        }
+        nodeLog_.resize(r.n_node_log);
+        nodeLogPos_ = 0;
+      }
       secondsPerExpandedNode_ =
           r.expanded_nodes > 0 ? 1e-3 * st.kernel_ms / static_cast<double>(r.expanded_nodes) : 0.;
       // mapUnmappedGates / mapToMinDistance also move the placed qubit in the

@@ -22,6 +22,12 @@
 #ifdef QMAP_DROPIN
 #include "../integration/GpuHeuristicMapper.hpp"
 using BaseMapper = GpuHeuristicMapper;
+// -DQMAP_DROPIN_EMU: the drop-in on the host debug build of the kernel source
+// (tests/emu/dropin_shim.cpp) instead of libqmap_b200.so, for containers
+// without a GPU; the shim takes the cost tables from the mapper's Architecture
+#ifdef QMAP_DROPIN_EMU
+extern "C" void qemu_shim_reference_architecture(const void* architecture);
+#endif
 #else
 using BaseMapper = HeuristicMapper;
 #endif
@@ -187,6 +193,9 @@ RefResult* runMap(RefArch* a, qc::QuantumComputation&& circ,
   if (logPath != nullptr && logPath[0] != '\0') {
     cfg.dataLoggingPath = logPath;
   }
+#ifdef QMAP_DROPIN_EMU
+  qemu_shim_reference_architecture(&a->arch);
+#endif
   const auto t0 = std::chrono::steady_clock::now();
   res->mapper->run(cfg);
   const auto t1 = std::chrono::steady_clock::now();
