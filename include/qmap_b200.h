@@ -284,6 +284,39 @@ int qmg_circuit_batch_layers(const qmg_circuit_batch* batch, size_t i,
                              qmg_layers* out);
 void qmg_circuit_batch_destroy(qmg_circuit_batch* batch);
 
+/*
+ * OpenQASM 2 reader for the gate set of the reference's example circuits
+ * (qreg / creg, cx, one-qubit gates with parameter expressions, measure,
+ * barrier; SURVEY section 8 row f2: inputs of 10^5 .. 10^6 gates).  The
+ * reference delegates reading to mqt-core's qasm3::Importer::importf
+ * (test/sc/heuristic/test_heuristic.cpp:253) and strips idle qubits in
+ * Mapper's constructor (src/sc/Mapper.cpp:33-53); qmg_qasm_mapper_view gives
+ * the gate operands as createLayers then reads them (Mapper.cpp:166-172) and
+ * the InitialLayout::Identity placement (HeuristicMapper.cpp:176-183), ready
+ * for qmg_circuit_create / qmg_circuit_batch_create.  Unsupported gates fail
+ * with the reference's message (Mapper.cpp:157-161) in qmg_last_error().
+ */
+typedef struct qmg_qasm qmg_qasm;
+typedef struct {
+  uint32_t n_qubits, n_clbits;
+  uint64_t n_gates, n_measurements;
+} qmg_qasm_info;
+int qmg_qasm_read_file(const char* path, qmg_qasm** out);
+int qmg_qasm_parse(const char* text, size_t length, qmg_qasm** out);
+int qmg_qasm_get_info(const qmg_qasm* q, qmg_qasm_info* info);
+/* gate i: control[i] (-1: one-qubit gate), target[i], kind[i] (see
+ * qmg_qasm_gate_name), params[3 i .. 3 i + 2] and n_params[i]; any output
+ * pointer may be NULL */
+int qmg_qasm_gates(const qmg_qasm* q, int32_t* control, int32_t* target,
+                   uint8_t* kind, double* params, uint8_t* n_params);
+int qmg_qasm_measurements(const qmg_qasm* q, uint32_t* qubit, uint32_t* clbit);
+/* operands renumbered over the qubits that are not idle; identity_locations
+ * (nPhysical entries, may be NULL): p for every used original index p, else -1 */
+int qmg_qasm_mapper_view(const qmg_qasm* q, uint32_t nPhysical, int32_t* control,
+                         int32_t* target, int16_t* identity_locations);
+const char* qmg_qasm_gate_name(uint8_t kind); /* NULL beyond the last kind */
+void qmg_qasm_destroy(qmg_qasm* q);
+
 /* one search unit: a circuit, a start layout and a pass schedule */
 typedef struct {
   qmg_layers layers;

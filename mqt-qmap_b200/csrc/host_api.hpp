@@ -4,6 +4,8 @@
 #pragma once
 #include <cstring>
 #include <exception>
+#include <fstream>
+#include <iterator>
 #include <atomic>
 #include <memory>
 #include <mutex>
@@ -14,6 +16,7 @@
 #include "flat_layers.hpp"
 #include "flatten.hpp"
 #include "layers.hpp"
+#include "qasm_reader.hpp"
 
 namespace qmg {
 inline std::string& lastError() {
@@ -84,6 +87,10 @@ struct qmg_circuit {
 // createLayers of many circuits at once, CSR only (flat_layers.hpp)
 struct qmg_circuit_batch {
   std::vector<qmg::FlatLayers> circ;
+};
+
+struct qmg_qasm {
+  qmg::QasmCircuit c;
 };
 
 #define QMG_API extern "C" __attribute__((visibility("default")))
@@ -370,4 +377,97 @@ QMG_API int qmg_circuit_batch_verify(const qmg_circuit_batch* b, uint16_t n,
   });
   return QMG_OK;
 }
+// ---- OpenQASM 2 reader (qasm_reader.hpp)
+QMG_API int qmg_qasm_parse(const char* text, size_t length, qmg_qasm** out) {
+  if (text == nullptr || out == nullptr) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  try {
+    auto q = std::make_unique<qmg_qasm>();
+    q->c.parse(text, length);
+    *out = q.release();
+    return QMG_OK;
+  } catch (const std::exception& e) {
+    return qmg::fail(QMG_BAD_ARG, e.what());
+  }
+}
+QMG_API int qmg_qasm_read_file(const char* path, qmg_qasm** out) {
+  if (path == nullptr || out == nullptr) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  std::ifstream f(path, std::ios::binary);
+  if (!f) {
+    return qmg::fail(QMG_BAD_ARG, std::string("cannot open ") + path);
+  }
+  std::string text((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+  return qmg_qasm_parse(text.data(), text.size(), out);
+}
+QMG_API int qmg_qasm_get_info(const qmg_qasm* q, qmg_qasm_info* info) {
+  if (q == nullptr || info == nullptr) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  info->n_qubits = q->c.nQubits;
+  info->n_clbits = q->c.nClbits;
+  info->n_gates = q->c.kind.size();
+  info->n_measurements = q->c.measQubit.size();
+  return QMG_OK;
+}
+QMG_API int qmg_qasm_gates(const qmg_qasm* q, int32_t* control, int32_t* target,
+                           uint8_t* kind, double* params, uint8_t* n_params) {
+  if (q == nullptr) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  const size_t g = q->c.kind.size();
+  if (g == 0) {
+    return QMG_OK;
+  }
+  if (control != nullptr) {
+    std::memcpy(control, q->c.control.data(), g * sizeof(int32_t));
+  }
+  if (target != nullptr) {
+    std::memcpy(target, q->c.target.data(), g * sizeof(int32_t));
+  }
+  if (kind != nullptr) {
+    std::memcpy(kind, q->c.kind.data(), g);
+  }
+  if (params != nullptr) {
+    std::memcpy(params, q->c.params.data(), 3 * g * sizeof(double));
+  }
+  if (n_params != nullptr) {
+    std::memcpy(n_params, q->c.nParams.data(), g);
+  }
+  return QMG_OK;
+}
+QMG_API int qmg_qasm_measurements(const qmg_qasm* q, uint32_t* qubit, uint32_t* clbit) {
+  if (q == nullptr) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  const size_t m = q->c.measQubit.size();
+  if (m != 0 && qubit != nullptr) {
+    std::memcpy(qubit, q->c.measQubit.data(), m * sizeof(uint32_t));
+  }
+  if (m != 0 && clbit != nullptr) {
+    std::memcpy(clbit, q->c.measClbit.data(), m * sizeof(uint32_t));
+  }
+  return QMG_OK;
+}
+QMG_API int qmg_qasm_mapper_view(const qmg_qasm* q, uint32_t nPhysical,
+                                 int32_t* control, int32_t* target,
+                                 int16_t* identity_locations) {
+  if (q == nullptr || ((control == nullptr || target == nullptr) && !q->c.kind.empty())) {
+    return qmg::fail(QMG_BAD_ARG, "null argument");
+  }
+  try {
+    q->c.mapperView(nPhysical, control, target, identity_locations);
+    return QMG_OK;
+  } catch (const std::exception& e) {
+    return qmg::fail(QMG_BAD_ARG, e.what());
+  }
+}
+QMG_API const char* qmg_qasm_gate_name(uint8_t kind) {
+  size_t cnt = 0;
+  const char* const* names = qmg::qasmGateNames(&cnt);
+  return kind < cnt ? names[kind] : nullptr;
+}
+QMG_API void qmg_qasm_destroy(qmg_qasm* q) { delete q; }
 #endif

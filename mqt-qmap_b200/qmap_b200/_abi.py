@@ -153,9 +153,16 @@ EXPORTS = [
     "qmg_circuit_batch_create", "qmg_circuit_batch_layers", "qmg_circuit_batch_destroy",
     "qmg_circuit_batch_fill_instances", "qmg_circuit_batch_layer_gates",
     "qmg_circuit_batch_verify",
+    "qmg_qasm_read_file", "qmg_qasm_parse", "qmg_qasm_get_info", "qmg_qasm_gates",
+    "qmg_qasm_measurements", "qmg_qasm_mapper_view", "qmg_qasm_gate_name", "qmg_qasm_destroy",
 ]
 
 _lib = None
+
+
+class QmgQasmInfo(C.Structure):
+    _fields_ = [("n_qubits", C.c_uint32), ("n_clbits", C.c_uint32),
+                ("n_gates", C.c_uint64), ("n_measurements", C.c_uint64)]
 
 
 def bind_host_api(L):
@@ -180,6 +187,16 @@ def bind_host_api(L):
                                            C.c_void_p]
     L.qmg_circuit_batch_destroy.argtypes = [C.c_void_p]
     L.qmg_circuit_batch_destroy.restype = None
+    L.qmg_qasm_read_file.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.qmg_qasm_parse.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_void_p)]
+    L.qmg_qasm_get_info.argtypes = [C.c_void_p, C.POINTER(QmgQasmInfo)]
+    L.qmg_qasm_gates.argtypes = [C.c_void_p] * 6
+    L.qmg_qasm_measurements.argtypes = [C.c_void_p] * 3
+    L.qmg_qasm_mapper_view.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.qmg_qasm_gate_name.argtypes = [C.c_uint8]
+    L.qmg_qasm_gate_name.restype = C.c_char_p
+    L.qmg_qasm_destroy.argtypes = [C.c_void_p]
+    L.qmg_qasm_destroy.restype = None
 
 
 def load(path: str = LIB_PATH):

@@ -6,6 +6,7 @@ qasm3::Importer, which are outside the accelerated path.)
 from __future__ import annotations
 
 import math
+import os
 import re
 from dataclasses import dataclass, field
 
@@ -248,6 +249,92 @@ def parse_qasm(text: str, name: str = "circuit") -> Circuit:
     circ.n_qubits = nq
     circ.n_clbits = nc
     return circ
+
+
+class NativeQasm:
+    """A circuit read by the library's own OpenQASM 2 reader (qmg_qasm_*,
+    csrc/qasm_reader.hpp; the host C++ side of large inputs): gate arrays
+    without a Python object per gate.  `lib` is the loaded C ABI (_abi.load())."""
+
+    def __init__(self, lib, path: str = None, text: str = None):
+        import ctypes as C
+        from . import _abi
+        self.lib = lib
+        h = C.c_void_p()
+        if path is not None:
+            _abi.check(lib, lib.qmg_qasm_read_file(os.fsencode(path), C.byref(h)))
+        else:
+            raw = text.encode()
+            _abi.check(lib, lib.qmg_qasm_parse(raw, len(raw), C.byref(h)))
+        self.h = h
+        info = _abi.QmgQasmInfo()
+        _abi.check(lib, lib.qmg_qasm_get_info(h, C.byref(info)))
+        self.n_qubits, self.n_clbits = int(info.n_qubits), int(info.n_clbits)
+        self.n_gates, self.n_measurements = int(info.n_gates), int(info.n_measurements)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.qmg_qasm_destroy(self.h)
+            self.h = None
+
+    def gate_arrays(self):
+        """(control, target) as Circuit.gate_arrays()."""
+        from . import _abi
+        c = np.empty(self.n_gates, dtype=np.int32)
+        t = np.empty(self.n_gates, dtype=np.int32)
+        _abi.check(self.lib, self.lib.qmg_qasm_gates(self.h, c.ctypes.data, t.ctypes.data, None, None, None))
+        return c, t
+
+    def gates(self):
+        """(control, target, kind, params[g, 3], n_params) and the kind names."""
+        from . import _abi
+        g = self.n_gates
+        c, t = np.empty(g, np.int32), np.empty(g, np.int32)
+        k, npar = np.empty(g, np.uint8), np.empty(g, np.uint8)
+        p = np.empty((g, 3), np.float64)
+        _abi.check(self.lib, self.lib.qmg_qasm_gates(self.h, c.ctypes.data, t.ctypes.data, k.ctypes.data,
+                                                     p.ctypes.data, npar.ctypes.data))
+        names = []
+        while True:
+            nm = self.lib.qmg_qasm_gate_name(len(names))
+            if nm is None:
+                break
+            names.append(nm.decode())
+        return c, t, k, p, npar, names
+
+    def measurements(self):
+        from . import _abi
+        q = np.empty(self.n_measurements, np.uint32)
+        c = np.empty(self.n_measurements, np.uint32)
+        _abi.check(self.lib, self.lib.qmg_qasm_measurements(self.h, q.ctypes.data, c.ctypes.data))
+        return q, c
+
+    def mapper_view(self, n_physical: int):
+        """(control, target, identity_locations) as Circuit.mapper_view()."""
+        from . import _abi
+        c = np.empty(self.n_gates, dtype=np.int32)
+        t = np.empty(self.n_gates, dtype=np.int32)
+        ident = np.empty(n_physical, dtype=np.int16)
+        _abi.check(self.lib, self.lib.qmg_qasm_mapper_view(self.h, n_physical, c.ctypes.data, t.ctypes.data,
+                                                           ident.ctypes.data))
+        return c, t, ident
+
+    def to_circuit(self, name: str = "circuit") -> Circuit:
+        c, t, k, p, npar, names = self.gates()
+        circ = Circuit(self.n_qubits, name=name, n_clbits=self.n_clbits)
+        for i in range(self.n_gates):
+            if c[i] >= 0:
+                circ.ops.append(Op(names[k[i]], (int(c[i]), int(t[i]))))
+            else:
+                circ.ops.append(Op(names[k[i]], (int(t[i]),), tuple(float(x) for x in p[i, :npar[i]])))
+        q, cl = self.measurements()
+        circ.measurements = [(int(a), int(b)) for a, b in zip(q, cl)]
+        return circ
+
+
+def load_qasm_native(lib, path: str) -> NativeQasm:
+    """The file through the library's reader (fails like parse_qasm does)."""
+    return NativeQasm(lib, path=path)
 
 
 def load_qasm(path: str) -> Circuit:

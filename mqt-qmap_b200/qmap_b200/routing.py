@@ -186,6 +186,17 @@ class CircuitBatch:
             if gate_lists else np.zeros(0, np.int32)
         return cls(lib, n_arch_qubits, off, ctrl, tgt, layering)
 
+    @classmethod
+    def from_qasm_files(cls, lib, n_arch_qubits, paths, layering=0):
+        """Files -> layers without a Python object per gate: the library's
+        OpenQASM 2 reader (qmg_qasm_*), the mapper's view of each circuit
+        (idle qubits stripped) and createLayers of the whole batch.  Returns
+        (batch, [identity initial locations per circuit])."""
+        from . import circuit as qcirc
+        views = [qcirc.load_qasm_native(lib, p).mapper_view(n_arch_qubits) for p in paths]
+        batch = cls.from_gate_lists(lib, n_arch_qubits, [(c, t) for c, t, _ in views], layering)
+        return batch, [ident for _, _, ident in views]
+
     def __len__(self):
         return len(self.offsets) - 1
 

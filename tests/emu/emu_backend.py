@@ -30,7 +30,7 @@ def build(asan: bool = False) -> str:
     src = os.path.join(HERE, "emu.cpp")
     deps = [src] + [os.path.join(ROOT, "mqt-qmap_b200", "csrc", f)
                     for f in ("route_core.hpp", "layers.hpp", "host_api.hpp", "flatten.hpp",
-                              "dijkstra_core.hpp", "flat_layers.hpp")]
+                              "dijkstra_core.hpp", "flat_layers.hpp", "qasm_reader.hpp")]
     deps.append(os.path.join(ROOT, "include", "qmap_b200.h"))
     if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
         return out

@@ -305,3 +305,99 @@ def _connected(a, subset):
                 seen.add(v)
                 todo.append(v)
     return seen == s
+
+
+# ---------------------------------------------------------------------------
+# the library's OpenQASM 2 reader (csrc/qasm_reader.hpp, qmg_qasm_*) against
+# the Python reader (qmap_b200/circuit.py), which the golden runs pin to the
+# reference's own import of the same files
+# ---------------------------------------------------------------------------
+def _qasm_files():
+    import glob
+    files = sorted(glob.glob(os.path.join(parity.CIRCUITS, "*.qasm")))
+    full = os.path.join(os.path.dirname(parity.CIRCUITS), "circuits_full")
+    big = sorted(glob.glob(os.path.join(full, "*.qasm")), key=os.path.getsize)
+    return files + big[:60] + big[-3:]
+
+
+def test_native_qasm_reader_equals_the_python_reader():
+    from qmap_b200 import circuit as qc
+    L = _abi.load()
+    n_gates = 0
+    for path in _qasm_files():
+        want = qc.load_qasm(path)
+        got = qc.load_qasm_native(L, path)
+        assert (got.n_qubits, got.n_clbits, got.n_gates) == (want.n_qubits, want.n_clbits, len(want.ops)), path
+        wc, wt = want.gate_arrays()
+        c, t, k, p, npar, names = got.gates()
+        assert np.array_equal(c, wc) and np.array_equal(t, wt), path
+        assert [names[i] for i in k] == [o.name for o in want.ops], path
+        for i in np.nonzero(npar)[0]:
+            assert tuple(p[i, :npar[i]]) == tuple(want.ops[i].params), (path, i)   # bit for bit
+        assert all(len(o.params) == npar[i] for i, o in enumerate(want.ops)), path
+        for n_phys in (want.n_qubits, 27):
+            a, b = got.mapper_view(n_phys), want.mapper_view(n_phys)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b)), path
+        n_gates += got.n_gates
+    assert n_gates > 10000
+
+
+def test_native_qasm_reader_statements_and_errors():
+    from qmap_b200 import circuit as qc
+    L = _abi.load()
+    text = """OPENQASM 2.0; include "qelib1.inc";  // header
+    qreg a[2]; qreg b[3]; creg c[5]; creg d[1];
+    h a[0]; CX a[1],b[2]; cx b[0] , a[0];
+    u3(pi/2, -pi/4 , 0.25e1) b[1];  rz( (1+2)*pi/8 - 3/4 ) b[2]; u1(-(pi)) a[1]; u2(0,pi) a[0];
+    barrier a[0],b[1];
+    measure b -> c; measure a[1] -> d[0];
+    t b[2]; // trailing comment
+    """
+    want = qc.parse_qasm(text)
+    got = qc.NativeQasm(L, text=text)
+    circ = got.to_circuit()
+    assert (circ.n_qubits, circ.n_clbits) == (want.n_qubits, want.n_clbits) == (5, 6)
+    assert [(o.name, o.qubits, o.params) for o in circ.ops] == [(o.name, o.qubits, o.params) for o in want.ops]
+    assert circ.measurements == want.measurements == [(2, 0), (3, 1), (4, 2), (1, 5)]
+    # qubit 4 = b[2] is used, everything is: identity on 5 of 8 physical qubits
+    assert got.mapper_view(8)[2].tolist() == [0, 1, 2, 3, 4, -1, -1, -1]
+    # an idle qubit in the middle moves the logical indices above it down (Mapper.cpp:44-53)
+    idle = qc.NativeQasm(L, text="qreg q[4]; cx q[0],q[3]; h q[1];")
+    c, t, ident = idle.mapper_view(5)
+    assert (c.tolist(), t.tolist(), ident.tolist()) == ([0, -1], [2, 1], [0, 1, -1, 3, -1])
+    w = qc.parse_qasm("qreg q[4]; cx q[0],q[3]; h q[1];").mapper_view(5)
+    assert (w[0].tolist(), w[1].tolist(), w[2].tolist()) == ([0, -1], [2, 1], [0, 1, -1, 3, -1])
+    for bad, msg in (("qreg q[3]; ccx q[0],q[1],q[2];", "more than one control or an unsupported gate \\(ccx\\)"),
+                     ("qreg q[2]; cx q[0];", "bad cx"),
+                     ("qreg q[2]; h q[0],q[1];", "bad 1q gate"),
+                     ("qreg q[2]; h r[0];", "bad qubit argument"),
+                     ("qreg q[2]; rz(pi//2) q[0];", "parse"),
+                     ("qreg q[2]; rz(2*) q[0];", "parse")):
+        with pytest.raises(_abi.QmapError, match=msg):
+            qc.NativeQasm(L, text=bad)
+        with pytest.raises((ValueError, IndexError)):
+            qc.parse_qasm(bad)
+    with pytest.raises(_abi.QmapError, match="SWAP gates"):
+        qc.NativeQasm(L, text="qreg q[2]; swap q[0],q[1];").mapper_view(2)
+    with pytest.raises(_abi.QmapError, match="cannot open"):
+        qc.load_qasm_native(L, "/nonexistent/x.qasm")
+
+
+def test_circuit_batch_from_qasm_files_equals_the_python_path():
+    """Files -> CSR layers through the library alone (qmg_qasm_read_file,
+    qmg_qasm_mapper_view, qmg_circuit_batch_create) against the Python reader
+    + qmg_circuit_create."""
+    L = _abi.load()
+    paths = _qasm_files()[:30]
+    n = 27
+    for layering in (0, 1, 4):
+        batch, idents = routing.CircuitBatch.from_qasm_files(L, n, paths, layering)
+        assert len(batch) == len(paths)
+        for i, p in enumerate(paths):
+            c, t, ident = qcirc.load_qasm(p).mapper_view(n)
+            assert np.array_equal(idents[i], ident), p
+            one = routing.LayeredCircuit(L, n, c, t, layering)
+            a, b = _layers_arrays(batch[i].layers), _layers_arrays(one.layers)
+            assert a[0] == b[0] and a[1] == b[1], p
+            for x, y in zip(a[2:], b[2:]):
+                assert np.array_equal(x, y), p
