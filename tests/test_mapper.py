@@ -100,3 +100,41 @@ def test_verifier_rejects_a_wrong_circuit():
     k = next(i for i, o in enumerate(m.mapped_ops) if o.name == "swap")
     del m.mapped_ops[k]
     assert mapper.verify_mapping(circ, m) != ""
+
+
+def test_compile_mirrors_the_reference_entry_point():
+    """qmap_b200.compile (python/mqt/qmap/compile.py:59-171): argument names
+    and defaults of the reference, SWAP counts of its committed outputs."""
+    import inspect
+    import qmap_b200
+    sig = inspect.signature(qmap_b200.compile)
+    want = ["circ", "arch", "calibration", "method", "heuristic", "initial_layout",
+            "iterative_bidirectional_routing_passes", "layering", "automatic_layer_splits_node_limit",
+            "early_termination", "early_termination_limit", "lookahead_heuristic", "lookaheads",
+            "lookahead_factor", "encoding", "commander_grouping", "swap_reduction", "swap_limit",
+            "include_WCNF", "use_subsets", "subgraph", "pre_mapping_optimizations",
+            "post_mapping_optimizations", "add_measurements_to_mapped_circuit",
+            "add_barriers_between_layers", "verbose", "debug", "visualizer"]
+    assert list(sig.parameters)[:len(want)] == want
+    assert sig.parameters["automatic_layer_splits_node_limit"].default == 5000
+    assert sig.parameters["lookaheads"].default == 15 and sig.parameters["lookahead_factor"].default == 0.5
+    with pytest.raises(ValueError, match="Either arch or calibration must be specified"):
+        qmap_b200.compile("qreg q[1];", None)
+    a, be = arch_and_backend("ibm_qx5")
+    with pytest.raises(_abi.QmapError, match="not part of this library"):
+        qmap_b200.compile("qreg q[1];", a, method="exact", lib=be.lib, backend=be)
+    n = 0
+    for g in CASES:
+        cfg = g.meta["config"]
+        if g.meta["arch"] != "ibm_qx5" or g.meta["split"] or set(cfg) - {"heuristic", "lookahead_heuristic",
+                                                                        "layering", "initial_layout"}:
+            continue
+        path = os.path.join(parity.CIRCUITS, g.meta["circuit"])
+        kw = dict(cfg)
+        if kw.get("lookahead_heuristic") == "none":
+            kw["lookahead_heuristic"] = None
+        mapped, res = qmap_b200.compile(path, a, lib=be.lib, backend=be, **kw)
+        assert res.output_swaps == g.swaps, g.label
+        assert mapped.n_qubits == 16 and len(mapped.ops) == res.output_gates
+        n += 1
+    assert n >= 5
