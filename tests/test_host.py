@@ -339,7 +339,7 @@ def test_native_qasm_reader_equals_the_python_reader():
             a, b = got.mapper_view(n_phys), want.mapper_view(n_phys)
             assert all(np.array_equal(x, y) for x, y in zip(a, b)), path
         n_gates += got.n_gates
-    assert n_gates > 10000
+    assert n_gates > 3000  # (the committed subset alone has 3717 gates)
 
 
 def test_native_qasm_reader_statements_and_errors():
