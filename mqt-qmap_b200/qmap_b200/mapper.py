@@ -45,6 +45,105 @@ class MappingResults:
     layer_n_swaps: np.ndarray | None = None
     config: object = None
     extras: dict = field(default_factory=dict)
+    # CircuitInfo / statistics as MappingResults::json() reports them
+    input_name: str = ""
+    input_qubits: int = 0
+    output_name: str = ""
+    output_qubits: int = 0
+    architecture: str = ""
+    timeout: bool = True
+    total_fidelity: float = 1.0
+    total_log_fidelity: float = 0.0
+    # heuristicBenchmark (filled with config.debug, HeuristicMapper.cpp:432-444)
+    average_branching_factor: float = 0.0
+    effective_branching_factor: float = 0.0
+    seconds_per_node: float = 0.0
+    layer_benchmark: np.ndarray | None = None  # per-layer records (debug)
+
+    def json(self) -> dict:
+        """MappingResults::json() (include/sc/MappingResults.hpp:127-175) with
+        Configuration::json() (src/sc/Configuration.cpp:24-78)."""
+        cfg = self.config
+
+        def name(table, v):
+            return next(k for k, x in table.items() if x == v)
+
+        heur = name(_abi.HEURISTICS, cfg.heuristic)
+        fid = heur == "fidelity_best_location"
+        settings = {
+            "heuristic": heur,
+            # isAdmissible / isPrincipallyAdmissible / isTight / isFidelityAware
+            # (include/sc/configuration/Heuristic.hpp:44-126)
+            "heuristic_properties": {
+                "admissible": heur in ("gate_count_max_distance", "fidelity_best_location"),
+                "principally_admissible": heur != "gate_count_sum_distance",
+                "tight": not fid,
+                "fidelity_aware": fid,
+            },
+            "initial_layout": name(_abi.LAYOUTS, cfg.initial_layout),
+        }
+        if cfg.lookahead_heuristic != _abi.LOOKAHEADS["none"]:
+            settings["lookahead"] = {
+                "heuristic": name(_abi.LOOKAHEADS, cfg.lookahead_heuristic),
+                "heuristic_properties": {"fidelity_aware": False},
+                "lookaheads": int(cfg.nr_lookaheads),
+                "first_factor": float(cfg.first_lookahead_factor),
+                "factor": float(cfg.lookahead_factor),
+            }
+        return {
+            "circuit": {"name": self.input_name, "qubits": self.input_qubits, "gates": self.input_gates,
+                        "single_qubit_gates": self.input_single_qubit_gates, "cnots": self.input_cnots},
+            "mapped_circuit": {"name": self.output_name, "qubits": self.output_qubits,
+                               "gates": self.output_gates,
+                               "single_qubit_gates": self.output_single_qubit_gates,
+                               "cnots": self.output_cnots},
+            "config": {
+                "method": "heuristic",
+                "layering_strategy": name(_abi.LAYERINGS, cfg.layering),
+                "pre_mapping_optimizations": bool(cfg.pre_mapping_optimizations),
+                "post_mapping_optimizations": bool(cfg.post_mapping_optimizations),
+                "add_measurements_to_mapped_circuit": bool(cfg.add_measurements_to_mapped_circuit),
+                "verbose": bool(cfg.verbose),
+                "debug": bool(cfg.debug),
+                "settings": settings,
+            },
+            "statistics": {
+                "timeout": self.timeout,
+                "mapping_time": self.time,
+                "arch": self.architecture,
+                "layers": self.input_layers,
+                "swaps": self.output_swaps,
+                "total_fidelity": self.total_fidelity,
+                "total_log_fidelity": self.total_log_fidelity,
+                "benchmark": {
+                    "expanded_nodes": self.expanded_nodes if cfg.debug else 0,
+                    "generated_nodes": self.generated_nodes if cfg.debug else 0,
+                    "seconds_per_node": self.seconds_per_node,
+                    "average_branching_factor": self.average_branching_factor,
+                    "effective_branching_factor": self.effective_branching_factor,
+                },
+                "additional_gates": self.output_gates - self.input_gates,
+            },
+        }
+
+
+def effective_branching_rate(nodes_processed: int, solution_depth: int) -> float:
+    """HeuristicMapper::computeEffectiveBranchingRate (HeuristicMapper.hpp:411-435)."""
+    if solution_depth == 0:
+        return 0.0
+    nodes_processed -= 1
+    upper = float(nodes_processed) ** (1.0 / solution_depth)
+    lower = upper / solution_depth
+    while upper - lower > 2e-10:
+        mid = (lower + upper) / 2.0
+        total = 0.0
+        for i in range(1, solution_depth + 1):
+            total += mid ** i
+        if total < nodes_processed:
+            lower = mid
+        else:
+            upper = mid
+    return (lower + upper) / 2.0
 
 
 class HeuristicMapper:
@@ -162,14 +261,15 @@ class HeuristicMapper:
         extra = len(c) if cfg.automatic_layer_splits and library_splits else 0
         passes = int(cfg.iterative_bidirectional_routing_passes)
         first = 0
-        lq_parts, ns_parts, swap_parts, place_parts = [], [], [], []
+        lq_parts, ns_parts, swap_parts, place_parts, rec_parts = [], [], [], [], []
         start_locations = None
         splits = 0
         while True:
             item = routing.RouteItem(lc, init, passes, first_layer=first)
             log_cap = self.node_log_capacity if self.data_logging_path else 0
-            out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True, lean=True,
-                                      extra_layers=extra, node_log_capacity=log_cap)[0]
+            out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True,
+                                      lean=not cfg.debug, extra_layers=extra,
+                                      node_log_capacity=log_cap)[0]
             if log_cap and out.status == _abi.QMG_OK and first == 0:
                 from . import datalog
                 datalog.write_node_logs(self.data_logging_path, out)
@@ -186,10 +286,16 @@ class HeuristicMapper:
             res.expanded_nodes_all_passes += out.expanded_nodes
             res.generated_nodes_all_passes += out.generated_nodes
             lq_parts.append(out.layer_qubits[first:done].copy())
-            ns_parts.append(out.layer_n_swaps[first:done].copy())
-            nsw = int(out.layer_n_swaps[first:done].sum())
-            swap_parts.append(out.swaps[:nsw].copy())
+            if out.layer_n_swaps is not None:  # lean outputs: packed SWAP lists
+                ns_parts.append(out.layer_n_swaps[first:done].copy())
+                nsw = int(out.layer_n_swaps[first:done].sum())
+                swap_parts.append(out.swaps[:nsw].copy())
+            else:  # full per-layer records (debug)
+                ns_parts.append(out.layers["n_swaps"][first:done].astype(np.uint16))
+                swap_parts.extend(out.layer_swaps(l).copy() for l in range(first, done))
             place_parts.append(out.placements.copy())
+            if cfg.debug and out.layers is not None:
+                rec_parts.append(out.layers[first:done].copy())
             if out.status == _abi.QMG_OK:
                 break
             if out.status != _abi.QMG_SPLIT_LIMIT_HIT:
@@ -208,10 +314,27 @@ class HeuristicMapper:
         res.layer_splits = splits
         res.input_layers = lc.n_layers
         res.layer_n_swaps = layer_n_swaps
+        # Mapper::initResults (Mapper.cpp:33-42)
+        res.input_name = self.qc.name
+        res.input_qubits = len(used)
+        res.output_name = self.qc.name + "_mapped"
+        res.output_qubits = n
+        res.architecture = self.architecture.name
+        if cfg.debug and rec_parts:
+            res.layer_benchmark = np.concatenate(rec_parts)
 
         self._emit(cfg, lc, c, t, n, start_given, start_locations, layer_qubits, layer_n_swaps,
                    swaps, placements, res)
+        # HeuristicMapper.cpp:432-444 (debug): totals over the final pass
+        if cfg.debug and res.expanded_nodes > 0:
+            res.average_branching_factor = (res.generated_nodes - lc.n_layers) / res.expanded_nodes
+            if res.layer_benchmark is not None:
+                for r in res.layer_benchmark:
+                    e = int(r["expanded_nodes"])
+                    res.effective_branching_factor += (
+                        effective_branching_rate(e + 1, int(r["solution_depth"])) * (e / res.expanded_nodes))
         res.time = time.perf_counter() - t_start
+        res.timeout = False
         self.results = res
         return res
 
@@ -331,9 +454,47 @@ class HeuristicMapper:
         self.mapped_ops = out_ops
         self.output_permutation = final_qubits
         self.initial_layout = initial
-        res.output_gates = sum(1 for o in out_ops if o.name != "barrier")
-        res.output_cnots = sum(1 for o in out_ops if len(o.qubits) == 2 and o.name != "swap")
-        res.output_single_qubit_gates = sum(1 for o in out_ops if len(o.qubits) == 1)
+        self._count_gates(out_ops, directed, res)
+
+    def _count_gates(self, out_ops, directed, res):
+        """Mapper::countGates (Mapper.cpp:532-585) over the mapped circuit: a
+        SWAP counts as 3 CNOTs on a bidirectional edge and as 3 CNOTs + 4 H on
+        a unidirectional one; with calibration data the -log2 fidelity costs
+        of all gates add up to total_log_fidelity."""
+        arch = self.architecture
+        fid = arch.fidelity_available
+        c1 = c2 = cs = None
+        if fid:
+            c1, c2, cs = (arch.single_qubit_fidelity_costs(), arch.two_qubit_fidelity_costs(),
+                          arch.swap_fidelity_costs())
+        gates = cnots = single = 0
+        log_fid = 0.0
+        for o in out_ops:
+            if o.name == "barrier":
+                continue
+            if o.name == "swap":
+                a, b = o.qubits
+                if fid:
+                    log_fid += float(cs[a][b])
+                cnots += 3
+                if (a, b) in directed and (b, a) in directed:
+                    gates += 3
+                else:
+                    gates += 7
+                    single += 4
+            elif len(o.qubits) == 1:
+                single += 1
+                gates += 1
+                if fid:
+                    log_fid += float(c1[o.qubits[0]])
+            else:
+                cnots += 1
+                gates += 1
+                if fid:
+                    log_fid += float(c2[o.qubits[0]][o.qubits[1]])
+        res.output_gates, res.output_cnots, res.output_single_qubit_gates = gates, cnots, single
+        res.total_log_fidelity = log_fid
+        res.total_fidelity = 2.0 ** (-log_fid)
 
     # ------------------------------------------------------------------
     def mapped_circuit(self) -> Circuit:

@@ -72,8 +72,10 @@ def test_static_and_identity_layouts():
         m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
         res = m.map(initial_layout=layout)
         assert mapper.verify_mapping(circ, m) == ""
-        assert res.output_cnots == res.input_cnots
-        assert res.output_gates == (res.input_gates + res.output_swaps
+        # Mapper::countGates: IBM QX5 is unidirectional - a SWAP is 3 CNOTs + 4 H,
+        # a reversed CNOT 4 H
+        assert res.output_cnots == res.input_cnots + 3 * res.output_swaps
+        assert res.output_gates == (res.input_gates + 7 * res.output_swaps
                                     + 4 * res.output_direction_reverse)
         out = m.mapped_circuit()
         again = qcirc.parse_qasm(out.to_qasm())
@@ -135,6 +137,48 @@ def test_compile_mirrors_the_reference_entry_point():
             kw["lookahead_heuristic"] = None
         mapped, res = qmap_b200.compile(path, a, lib=be.lib, backend=be, **kw)
         assert res.output_swaps == g.swaps, g.label
-        assert mapped.n_qubits == 16 and len(mapped.ops) == res.output_gates
+        assert mapped.n_qubits == 16 and len(mapped.ops) == res.output_gates - 6 * res.output_swaps
         n += 1
     assert n >= 5
+
+
+def _backend_with_calibration(name, calib):
+    n, e = parity.read_arch_file(name)
+    a = ar.Architecture().load_coupling_map(os.path.join(parity.ARCHS, name + ".arch"))
+    fid = None
+    if calib:
+        a.load_properties(os.path.join(parity.ARCHS, calib))
+        fid = (T[f"{name}_c1"], T[f"{name}_c2"], T[f"{name}_cswap"], T[f"{name}_fid"])
+    be = emu_backend.EmuBackend(n, e, T[f"{name}_dist"], T[f"{name}_dist_rev"], fid, pool_nodes=1 << 17)
+    return a, be
+
+
+def test_mapping_results_json_equals_the_reference():
+    """MappingResults::json() of the mirror against the compiled reference's:
+    circuit / mapped_circuit counts (Mapper::countGates), Configuration::json(),
+    swaps, layers, total (log) fidelity, the debug benchmark with average and
+    effective branching factors - everything but the two timing fields."""
+    import json
+    from oracle import refapi
+    R = parity.ref()
+    cases = [g for g in parity.golden_runs() if not g.meta["split"] and g.generated_nodes <= 20000]
+    picked = [g for g in cases if g.meta["calibration"]][::6] + [g for g in cases if not g.meta["calibration"]][::9]
+    assert len(picked) > 25
+    cache = {}
+    for g in picked:
+        m = g.meta
+        key = (m["arch"], m["calibration"])
+        if key not in cache:
+            files = (os.path.join(parity.ARCHS, m["arch"] + ".arch"),
+                     os.path.join(parity.ARCHS, m["calibration"]) if m["calibration"] else None)
+            cache[key] = _backend_with_calibration(*key) + (R.arch_load(*files),)
+        a, be, ra = cache[key]
+        path = os.path.join(parity.CIRCUITS, m["circuit"])
+        want = json.loads(R.map_qasm(ra, path, refapi.make_config(debug=True, **m["config"])).json)
+        circ = qcirc.load_qasm(path)
+        mp = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+        got = mp.map(debug=True, **m["config"]).json()
+        for j in (got, want):
+            j["statistics"].pop("mapping_time")
+            j["statistics"]["benchmark"].pop("seconds_per_node")
+        assert got == want, (g.label, got, want)
