@@ -9,14 +9,17 @@
 
 namespace qmg {
 
+// searches (warps) per CTA.  Measured on config 4 / config 2 (M nodes/s): 1 warp
+// per CTA, which makes the shared-memory base a constant, 41.0 / 154 against
+// 42.6 / 155 with 4; 12 warps per CTA (one CTA per SM for the fidelity kernel)
+// 47.4 / 152 against 45.9 / 153 - kept at 4
 #ifndef QMG_WARPS_PER_CTA
 #define QMG_WARPS_PER_CTA 4
 #endif
 constexpr int kWarpsPerCta = QMG_WARPS_PER_CTA;
 #ifndef QMG_MIN_CTAS
 // 6 CTAs (24 warps, 80 registers/thread) per SM measured best on config 2:
-// 3/4/5/6/8 -> 102/153/166/172/166 M nodes/s (the grid still holds 8 CTAs per
-// SM; the surplus CTAs start as earlier ones drain)
+// 3/4/5/6/8 -> 102/153/166/172/166 M nodes/s (round 1)
 #define QMG_MIN_CTAS 6
 #endif
 // upper bound of the per-warp working set (4 warps of a CTA must fit the
