@@ -402,8 +402,8 @@ class Architecture:
         return s
 
     def distance_table(self, include_reversal_cost=True) -> np.ndarray:
-        h = self.handle
         if self._dist is None:
+            h = self.handle
             n = self.n_qubits
             self._dist = np.empty((n, n))
             self._dist_rev = np.empty((n, n))
@@ -433,8 +433,8 @@ class Architecture:
 
     def fidelity_distance_tables(self) -> np.ndarray:
         self._need_fidelity()
-        h = self.handle
         if self._fid is None:
+            h = self.handle
             k = int(self.info().n_fidelity_tables)
             n = self.n_qubits
             self._fid = np.empty((k, n, n))

@@ -262,17 +262,19 @@ class HeuristicMapper:
         passes = int(cfg.iterative_bidirectional_routing_passes)
         first = 0
         lq_parts, ns_parts, swap_parts, place_parts, rec_parts = [], [], [], [], []
+        logged = None  # the routed instance whose node log was written
         start_locations = None
         splits = 0
         while True:
             item = routing.RouteItem(lc, init, passes, first_layer=first)
             log_cap = self.node_log_capacity if self.data_logging_path else 0
             out = routing.route_batch(backend, n, cfg, [item], want_layer_qubits=True,
-                                      lean=not cfg.debug, extra_layers=extra,
+                                      lean=not (cfg.debug or log_cap), extra_layers=extra,
                                       node_log_capacity=log_cap)[0]
             if log_cap and out.status == _abi.QMG_OK and first == 0:
                 from . import datalog
                 datalog.write_node_logs(self.data_logging_path, out)
+                logged = out
             if out.split_layers is not None and len(out.split_layers):
                 lc = lc.split_copy(out.split_layers)
                 splits += len(out.split_layers)
@@ -336,6 +338,10 @@ class HeuristicMapper:
         res.time = time.perf_counter() - t_start
         res.timeout = False
         self.results = res
+        if logged is not None:
+            # the rest of the DataLogger directory (architecture, layers, result)
+            from . import datalog
+            datalog.write_run(self.data_logging_path, self, logged, lc, c, t, res)
         return res
 
     # ------------------------------------------------------------------

@@ -182,3 +182,49 @@ def test_mapping_results_json_equals_the_reference():
             j["statistics"].pop("mapping_time")
             j["statistics"]["benchmark"].pop("seconds_per_node")
         assert got == want, (g.label, got, want)
+
+
+@pytest.mark.parametrize("arch,calib,heuristic", [
+    ("ibm_qx5", None, "gate_count_max_distance"),
+    ("ibmq_london", "ibmq_london.csv", "fidelity_best_location")])
+def test_data_logging_directory_equals_the_reference(arch, calib, heuristic, tmp_path):
+    """compile(..., visualizer=...) leaves what the reference's DataLogger
+    leaves (DataLogger.cpp): nodes_layer_<i>.csv line by line, layer_<i>.json,
+    architecture.json and mapping_result.json value by value (timing fields
+    aside); input.qasm / output.qasm exist (mqt-core's text is not pinned)."""
+    import json
+    import types
+    import qmap_b200
+    from oracle import refapi
+    R = parity.ref()
+    a, be = _backend_with_calibration(arch, calib)
+    a._dist, a._dist_rev = T[f"{arch}_dist"].copy(), T[f"{arch}_dist_rev"].copy()  # (no GPU here)
+    if calib:
+        a._fid = T[f"{arch}_fid"].copy()
+    files = (os.path.join(parity.ARCHS, arch + ".arch"), os.path.join(parity.ARCHS, calib) if calib else None)
+    ra = R.arch_load(*files)
+    for circuit in parity.DATALOG_CIRCUITS[:3]:
+        path = os.path.join(parity.CIRCUITS, circuit + ".qasm")
+        kw = dict(parity.DATALOG_CONFIG, heuristic=heuristic)
+        d_ref = str(tmp_path / (circuit + "_ref")) + os.sep
+        d_got = str(tmp_path / (circuit + "_got")) + os.sep
+        R.map_qasm(ra, path, refapi.make_config(**kw), d_ref)
+        ckw = {k: v for k, v in kw.items() if k != "automatic_layer_splits"}
+        ckw["lookahead_heuristic"] = None
+        ckw["automatic_layer_splits_node_limit"] = None
+        qmap_b200.compile(path, a, visualizer=types.SimpleNamespace(data_logging_path=d_got),
+                          lib=be.lib, backend=be, **ckw)
+        names = sorted(os.listdir(d_ref))
+        assert sorted(os.listdir(d_got)) == names
+        for f in names:
+            if f.endswith(".csv"):
+                assert open(d_got + f).read() == open(d_ref + f).read(), (circuit, f)
+            elif f.endswith(".json"):
+                x, y = json.load(open(d_got + f)), json.load(open(d_ref + f))
+                if f == "mapping_result.json":
+                    for j in (x, y):
+                        j["statistics"].pop("mapping_time")
+                        j["statistics"]["benchmark"].pop("seconds_per_node")
+                        for lb in j["statistics"]["benchmark"]["layers"]:
+                            lb.pop("seconds_per_node")
+                assert x == y, (circuit, f)
