@@ -1,0 +1,161 @@
+"""The reference's own Python tests of the heuristic mapper
+(test/python/test_heuristic_mapper.py:27-83), re-expressed for
+qmap_b200.compile: the same circuits on the same 5-qubit backend, `timeout`
+false, the SWAP count where the reference asserts one, and the mapped circuit
+checked by the replay verifier (the reference uses mqt.qcec, which is not part
+of it).  -m "not gpu": routed by the host build of the kernel source, cost
+tables from the compiled reference."""
+import numpy as np
+import pytest
+
+import emu_backend
+import parity
+import qmap_b200
+from qmap_b200 import architecture as ar
+from qmap_b200 import circuit as qcirc
+from qmap_b200 import mapper
+
+COUPLING = [(0, 1), (1, 0), (1, 2), (2, 1), (1, 3), (3, 1), (3, 4), (4, 3)]  # GenericBackendV2 of the fixture
+
+
+def emu_for(a):
+    """The host build of the kernel source for Architecture `a`: cost tables
+    from the compiled reference built on the same coupling map / error rates."""
+    ra = parity.ref().arch_create(a.n_qubits, a.coupling_map)
+    fid = None
+    if a.fidelity_available:
+        p = a.properties
+        q1 = [p.average_single_qubit_error_rate(q) if q in p.single_qubit_error else np.nan
+              for q in range(a.n_qubits)]
+        cx = [p.two_qubit_error.get(e, np.nan) for e in a.coupling_map]
+        ra.set_error_rates(q1, cx)
+        fid = (ra.single_qubit_fidelity_costs(), ra.two_qubit_fidelity_costs(), ra.swap_fidelity_costs(),
+               ra.fidelity_distance_tables())
+        assert np.array_equal(fid[0], a.single_qubit_fidelity_costs())   # (host -log2 costs, bit for bit)
+        assert np.array_equal(fid[1], a.two_qubit_fidelity_costs())
+        assert np.array_equal(fid[2], a.swap_fidelity_costs())
+    return emu_backend.EmuBackend(a.n_qubits, np.array(a.coupling_map, dtype=np.uint16).reshape(-1, 2),
+                                  ra.distance_table(False), ra.distance_table(True), fid, pool_nodes=1 << 14)
+
+
+@pytest.fixture(scope="module")
+def backend():
+    a = ar.Architecture(5, COUPLING)
+    return a, emu_for(a)
+
+
+def _circuit(n, gates):
+    c = qcirc.Circuit(n, n_clbits=n)
+    c.h(0)
+    for a, b in gates:
+        c.cx(a, b)
+    c.measurements = [(q, q) for q in range(n)]  # measure_all
+    return c
+
+
+def _compile_and_verify(backend, circ):
+    a, be = backend
+    mapped, results = qmap_b200.compile(circ, arch=a, lib=be.lib, backend=be)
+    assert results.timeout is False
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    m.map()
+    assert mapper.verify_mapping(circ, m) == ""
+    assert [(o.name, o.qubits) for o in m.mapped_ops] == [(o.name, o.qubits) for o in mapped.ops]
+    return results
+
+
+def test_heuristic_no_swaps_trivial_layout(backend):
+    _compile_and_verify(backend, _circuit(3, [(0, 1), (1, 2)]))
+
+
+def test_heuristic_no_swaps_non_trivial_layout(backend):
+    _compile_and_verify(backend, _circuit(4, [(0, 1), (0, 2), (0, 3)]))
+
+
+def test_heuristic_non_trivial_swaps(backend):
+    results = _compile_and_verify(backend, _circuit(3, [(0, 1), (1, 2), (2, 0)]))
+    assert results.output_swaps == 1
+
+
+# ---------------------------------------------------------------------------
+# test/python/test_compile.py:36-258 (the heuristic method)
+# ---------------------------------------------------------------------------
+def example_circuit():
+    return _circuit(3, [(0, 1), (1, 2)])
+
+
+def _compile_on(arch, calibration=None, **kw):
+    a = qmap_b200.compile.__globals__["load_architecture"](arch)
+    qmap_b200.compile.__globals__["load_calibration"](a, calibration)
+    be = emu_for(a)
+    circ = example_circuit()
+    mapped, results = qmap_b200.compile(circ, arch=a, lib=be.lib, backend=be, **kw)
+    assert results.timeout is False
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    m.map(results.config)
+    assert mapper.verify_mapping(circ, m) == ""
+    return mapped, results
+
+
+@pytest.mark.parametrize("arch", ["IBM_QX4", "IBM_QX5", "IBMQ_Yorktown", "IBMQ_London", "IBMQ_Bogota",
+                                  "IBMQ_Tokyo", "Rigetti_Agave", "Rigetti_Aspen"])
+def test_available_architectures_str(arch):
+    _compile_on(arch)
+
+
+def test_architecture_from_file(tmp_path):
+    f = tmp_path / "test_architecture.arch"
+    f.write_text("3\n0 1\n0 2\n1 2\n")
+    _compile_on(str(f))
+
+
+def test_architecture_from_python():
+    _compile_on(ar.Architecture(3, {(0, 1), (0, 2), (1, 2)}))
+
+
+def test_calibration_from_file(tmp_path):
+    f = tmp_path / "test_calibration.cal"
+    f.write_text('Header\nQ0,0,0,0,1e-2,1e-4,"0_1: 1e-2, 0_2: 1e-2"\nQ1,0,0,0,1e-2,1e-4,"1_2: 1e-2"\n'
+                 "Q2,0,0,0,1e-2,1e-4, \n")
+    _, results = _compile_on(None, calibration=str(f))
+    assert results.output_qubits == 3
+
+
+def test_parameters():
+    from qmap_b200 import _abi
+    properties = ar.Properties()
+    for q in range(3):
+        properties.set_single_qubit_error_rate(q, "x", 0.01)
+    for a, b in ((0, 1), (1, 0), (1, 2), (2, 1)):
+        properties.set_two_qubit_error_rate(a, b, 0.02)
+    arch = ar.Architecture(3, {(0, 1), (1, 0), (1, 2), (2, 1)}, properties)
+    _, results = _compile_on(
+        arch, method="heuristic", heuristic="gate_count_max_distance", initial_layout="dynamic",
+        iterative_bidirectional_routing_passes=1, layering="individual_gates",
+        automatic_layer_splits_node_limit=5000, lookahead_heuristic="gate_count_max_distance",
+        lookaheads=15, lookahead_factor=0.5, pre_mapping_optimizations=True,
+        post_mapping_optimizations=True, verbose=True, debug=True)
+    c = results.config
+    assert c.heuristic == _abi.HEURISTICS["gate_count_max_distance"]
+    assert c.lookahead_heuristic == _abi.LOOKAHEADS["gate_count_max_distance"]
+    assert c.initial_layout == _abi.LAYOUTS["dynamic"]
+    assert c.iterative_bidirectional_routing_passes == 1
+    assert c.layering == _abi.LAYERINGS["individual_gates"]
+    assert c.automatic_layer_splits == 1 and c.automatic_layer_splits_node_limit == 5000
+    assert c.nr_lookaheads == 15 and c.lookahead_factor == 0.5
+    assert c.pre_mapping_optimizations == 1 and c.post_mapping_optimizations == 1
+    assert c.verbose == 1 and c.debug == 1
+    _, results = _compile_on(
+        arch, method="heuristic", heuristic="fidelity_best_location", initial_layout="identity",
+        iterative_bidirectional_routing_passes=None, layering="disjoint_qubits",
+        automatic_layer_splits_node_limit=None, lookahead_heuristic=None,
+        pre_mapping_optimizations=False, post_mapping_optimizations=False, verbose=False, debug=False)
+    c = results.config
+    assert c.heuristic == _abi.HEURISTICS["fidelity_best_location"]
+    assert c.lookahead_heuristic == _abi.LOOKAHEADS["none"]
+    assert c.initial_layout == _abi.LAYOUTS["identity"]
+    assert c.iterative_bidirectional_routing_passes == 0
+    assert c.layering == _abi.LAYERINGS["disjoint_qubits"]
+    assert c.automatic_layer_splits == 0 and c.nr_lookaheads == 0
+    assert c.pre_mapping_optimizations == 0 and c.post_mapping_optimizations == 0
+    assert c.verbose == 0 and c.debug == 0
