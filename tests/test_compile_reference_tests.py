@@ -159,3 +159,51 @@ def test_parameters():
     assert c.automatic_layer_splits == 0 and c.nr_lookaheads == 0
     assert c.pre_mapping_optimizations == 0 and c.post_mapping_optimizations == 0
     assert c.verbose == 0 and c.debug == 0
+
+
+def test_layer_splitting_known_answer():
+    """HeuristicTestFidelity.LayerSplitting (test/sc/heuristic/test_heuristic.cpp:
+    1983-2141): a 3 x 4 grid with hand-picked error rates, one layer of 50 + 2
+    X gates and two CX blocks; a node limit of 1 forces splits until the layers
+    cannot be split any more.  Expected by the reference: 5 layers, 8 SWAPs and
+    the total log-fidelity written out below."""
+    import math
+    cm = set()
+    for r in range(3):
+        for c in range(4):
+            q = 4 * r + c
+            if c < 3:
+                cm |= {(q, q + 1), (q + 1, q)}
+            if r < 2:
+                cm |= {(q, q + 4), (q + 4, q)}
+    e5, e4, e3, e2, e1, e0 = 0.99, 0.9, 0.5, 0.4, 0.1, 0.01
+    props = ar.Properties()
+    for q, e in enumerate([e5, e5, e5, e5, e3, e3, e5, e3, e2, e1, e5, e2]):
+        props.set_single_qubit_error_rate(q, "x", e)
+    two = {(0, 1): e4, (1, 2): e4, (2, 3): e1, (0, 4): e5, (1, 5): e5, (2, 6): e4, (3, 7): e5,
+           (4, 5): e3, (5, 6): e5, (6, 7): e5, (4, 8): e0, (5, 9): e3, (6, 10): e1, (7, 11): e3,
+           (8, 9): e5, (9, 10): e4, (10, 11): e5}
+    for (a, b), e in two.items():
+        props.set_two_qubit_error_rate(a, b, e)
+        props.set_two_qubit_error_rate(b, a, e)
+    a = ar.Architecture(12, cm, props)
+    be = emu_for(a)
+    circ = qcirc.Circuit(12, n_clbits=12)
+    for _ in range(50):
+        circ.gate("x", 4)
+    circ.gate("x", 5)
+    circ.gate("x", 7)
+    for _ in range(5):
+        circ.cx(3, 0)
+        circ.cx(9, 2)
+    circ.measurements = [(q, q) for q in range(12)]
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    res = m.map(layering="disjoint_2q_blocks", initial_layout="identity", heuristic="fidelity_best_location",
+                lookahead_heuristic="none", pre_mapping_optimizations=False, post_mapping_optimizations=False,
+                swap_on_first_layer=True, automatic_layer_splits=True, automatic_layer_splits_node_limit=1)
+    assert mapper.verify_mapping(circ, m) == ""
+    assert res.input_layers == 5          # originally 1, split into 5 during A*
+    assert res.output_swaps == 8
+    c4, c3, c2, c1, c0 = (-math.log2(1 - e) for e in (e4, e3, e2, e1, e0))
+    expected = 3 * (c3 + c3 + c3 + c4 + c4 + c0 + c4 + c4) + 50 * c1 + c3 + c2 + 5 * c1 + 5 * c1
+    assert abs(res.total_log_fidelity - expected) < 1e-6
