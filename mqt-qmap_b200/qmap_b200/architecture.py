@@ -250,9 +250,13 @@ class Architecture:
         """spec: Properties, a path or CSV text (Architecture.cpp:94-189)."""
         if isinstance(spec, Properties):
             props = spec
-            if not self.coupling_map:
+            # Architecture.cpp:176-186: the coupling map follows from the
+            # properties only when no architecture is loaded (name and qubit
+            # count, isArchitectureAvailable)
+            if not (self.name and self.n_qubits):
                 self.coupling_map = sorted(props.two_qubit_error)
                 self.n_qubits = props.n_qubits
+                self.name = f"generic_{self.n_qubits}"
                 self._invalidate()
         else:
             if os.path.exists(spec):

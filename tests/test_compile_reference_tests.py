@@ -207,3 +207,58 @@ def test_layer_splitting_known_answer():
     c4, c3, c2, c1, c0 = (-math.log2(1 - e) for e in (e4, e3, e2, e1, e0))
     expected = 3 * (c3 + c3 + c3 + c4 + c4 + c0 + c4 + c4) + 50 * c1 + c3 + c2 + 5 * c1 + 5 * c1
     assert abs(res.total_log_fidelity - expected) < 1e-6
+
+
+def test_early_termination_known_answers():
+    """Functionality.earlyTermination (test_heuristic.cpp:1283-1362): x(0),
+    cx(1,2) on a 7-qubit line with calibration, fidelity-aware, limit 4: the
+    first layer's benchmark record under every termination strategy."""
+    cm = set()
+    for q in range(6):
+        cm |= {(q, q + 1), (q + 1, q)}
+    props = ar.Properties()
+    for q, e in enumerate([0.9, 0.5, 0.5, 0.5, 0.5, 0.5, 0.1]):
+        props.set_single_qubit_error_rate(q, "x", e)
+    for a, b in cm:
+        props.set_two_qubit_error_rate(a, b, 0.01)
+    arch = ar.Architecture(7, cm, props)
+    be = emu_for(arch)
+    circ = qcirc.Circuit(7, n_clbits=7)
+    circ.gate("x", 0)
+    circ.cx(1, 2)
+    circ.measurements = [(q, q) for q in range(7)]
+    base = dict(layering="disjoint_qubits", initial_layout="identity", automatic_layer_splits=False,
+                debug=True, heuristic="fidelity_best_location", lookahead_heuristic="none",
+                early_termination_limit=4)
+
+    def first_layer(strategy):
+        m = mapper.HeuristicMapper(circ, arch, lib=be.lib, backend=be)
+        res = m.map(early_termination=strategy, **base)
+        assert mapper.verify_mapping(circ, m) == ""
+        return res.layer_benchmark[0]
+
+    assert not first_layer("none")["early_termination"]
+    for strategy, field in (("expanded_nodes_after_first_solution", "expanded_nodes_after_first_solution"),
+                            ("expanded_nodes_after_current_optimal_solution", "expanded_nodes_after_optimal_solution"),
+                            ("expanded_nodes", "expanded_nodes"),
+                            ("solution_nodes", "solution_nodes"),
+                            ("solution_nodes_after_current_optimal_solution",
+                             "solution_nodes_after_optimal_solution")):
+        r = first_layer(strategy)
+        assert r["early_termination"] and r[field] == 4, strategy
+
+
+def test_invalid_settings():
+    """Functionality.InvalidSettings (test_heuristic.cpp:895-916)."""
+    props = ar.Properties()
+    props.set_single_qubit_error_rate(0, "x", 0.1)
+    arch = ar.Architecture(1, [], props)
+    be = emu_for(ar.Architecture(1, []))
+    circ = qcirc.Circuit(1)
+    circ.gate("x", 0)
+    m = mapper.HeuristicMapper(circ, arch, lib=be.lib, backend=be)
+    for bad in (dict(layering="odd_gates"), dict(layering="qubit_triangle"),
+                dict(layering="individual_gates", heuristic="fidelity_best_location")):
+        with pytest.raises(qmap_b200.QmapError):
+            m.map(heuristic=bad.pop("heuristic", "gate_count_max_distance"),
+                  lookahead_heuristic="gate_count_max_distance", **bad)
