@@ -262,3 +262,30 @@ def test_invalid_settings():
         with pytest.raises(qmap_b200.QmapError):
             m.map(heuristic=bad.pop("heuristic", "gate_count_max_distance"),
                   lookahead_heuristic="gate_count_max_distance", **bad)
+
+
+@pytest.mark.parametrize("layering,layers", [("disjoint_2q_blocks", 2), ("disjoint_qubits", 3),
+                                             ("individual_gates", 6)])
+def test_layering_known_answers(layering, layers):
+    """LayeringTest (test_heuristic.cpp:1450-1543): x(0) x(1) cx(0,1) cx(2,3)
+    cx(1,2) x(3) on a directed 4-qubit line; the number of layers per
+    strategy, and one barrier between consecutive layers (the reference's
+    count is one higher: mqt-core puts another barrier before the final
+    measurements)."""
+    arch = ar.Architecture(4, [(0, 1), (1, 2), (2, 3)])
+    be = emu_for(arch)
+    circ = qcirc.Circuit(4, n_clbits=4)
+    circ.gate("x", 0)
+    circ.gate("x", 1)
+    circ.cx(0, 1)
+    circ.cx(2, 3)
+    circ.cx(1, 2)
+    circ.gate("x", 3)
+    circ.measurements = [(q, q) for q in range(3)]
+    m = mapper.HeuristicMapper(circ, arch, lib=be.lib, backend=be)
+    res = m.map(layering=layering, initial_layout="dynamic", pre_mapping_optimizations=False,
+                post_mapping_optimizations=False, add_measurements_to_mapped_circuit=True,
+                add_barriers_between_layers=True, automatic_layer_splits=False)
+    assert res.input_layers == layers
+    assert sum(1 for o in m.mapped_ops if o.name == "barrier") == layers - 1
+    assert mapper.verify_mapping(circ, m) == ""
