@@ -289,3 +289,46 @@ def test_layering_known_answers(layering, layers):
     assert res.input_layers == layers
     assert sum(1 for o in m.mapped_ops if o.name == "barrier") == layers - 1
     assert mapper.verify_mapping(circ, m) == ""
+
+
+def test_heuristic_benchmark_known_answers():
+    """Functionality.HeuristicBenchmark (test_heuristic.cpp:777-856): three CX
+    on a 5-ring, identity layout, no lookahead - node counts, depths and
+    branching factors of both layers and of the run."""
+    cm = [(0, 1), (1, 0), (1, 2), (2, 1), (2, 3), (3, 2), (3, 4), (4, 3), (4, 0), (0, 4)]
+    arch = ar.Architecture(5, cm)
+    be = emu_for(arch)
+    circ = qcirc.Circuit(5, n_clbits=5)
+    circ.cx(4, 2)
+    circ.cx(3, 1)
+    circ.cx(4, 1)
+    circ.measurements = [(q, q) for q in range(5)]
+    m = mapper.HeuristicMapper(circ, arch, lib=be.lib, backend=be)
+    res = m.map(heuristic="gate_count_max_distance", layering="disjoint_qubits", initial_layout="identity",
+                pre_mapping_optimizations=False, post_mapping_optimizations=False,
+                lookahead_heuristic="none", debug=True)
+    lb = res.layer_benchmark
+    assert len(lb) == 2
+    assert (lb[0]["solution_depth"], lb[0]["generated_nodes"], lb[0]["expanded_nodes"]) == (1, 6, 1)
+    assert (lb[1]["solution_depth"], lb[1]["generated_nodes"], lb[1]["expanded_nodes"]) == (1, 5, 1)
+    for r, avg in ((lb[0], 5.0), (lb[1], 4.0)):
+        assert (int(r["generated_nodes"]) - 1) / int(r["expanded_nodes"]) == avg
+        assert abs(mapper.effective_branching_rate(int(r["expanded_nodes"]) + 1, int(r["solution_depth"])) - 1.0) < 1e-10
+    assert (res.generated_nodes, res.expanded_nodes) == (11, 2)
+    assert abs(res.average_branching_factor - 4.5) < 1e-10
+    assert abs(res.effective_branching_factor - 1.0) < 1e-10
+
+
+def test_benchmark_generated_nodes():
+    """Functionality.BenchmarkGeneratedNodes (test_heuristic.cpp:869-893):
+    cx(0,6) on IBM QX5 generates 30 nodes."""
+    a = ar.Architecture().load_coupling_map("IBM_QX5")
+    be = emu_for(a)
+    circ = qcirc.Circuit(16, n_clbits=16)
+    circ.cx(0, 6)
+    circ.measurements = [(q, q) for q in range(16)]
+    m = mapper.HeuristicMapper(circ, a, lib=be.lib, backend=be)
+    res = m.map(heuristic="gate_count_max_distance", lookahead_heuristic="none", layering="individual_gates",
+                automatic_layer_splits=False, initial_layout="identity", pre_mapping_optimizations=False,
+                post_mapping_optimizations=False, debug=True)
+    assert res.generated_nodes == 30 and res.layer_benchmark[0]["generated_nodes"] == 30
