@@ -205,6 +205,9 @@ struct QasmCircuit {
     const char* d = p;
     long idx = 0;
     while (p < e && *p >= '0' && *p <= '9') {
+      if (idx > 100000000L) {  // (far beyond any register; avoids overflow)
+        throw std::invalid_argument("index too large: '" + std::string(b, e) + "'");
+      }
       idx = idx * 10 + (*p - '0');
       ++p;
     }
@@ -256,7 +259,7 @@ struct QasmCircuit {
     auto qubitOf = [&](const char* b, const char* e) -> int32_t {
       const auto [name, idx] = regArg(b, e);
       const auto it = qregs.find(name);
-      if (it == qregs.end() || idx < 0) {
+      if (it == qregs.end() || idx < 0 || idx >= static_cast<long>(it->second.size)) {
         throw std::invalid_argument("bad qubit argument: '" + std::string(b, e) + "'");
       }
       return static_cast<int32_t>(it->second.first + idx);
@@ -285,6 +288,10 @@ struct QasmCircuit {
         const auto [name, size] = regArg(w, e);
         if (size < 0) {
           badStatement(b, e);
+        }
+        if (static_cast<uint64_t>(head == "qreg" ? nQubits : nClbits) + static_cast<uint64_t>(size) >
+            (1ULL << 24)) {
+          throw std::invalid_argument("register too large: '" + std::string(b, e) + "'");
         }
         if (head == "qreg") {
           qregs[name] = Reg{nQubits, static_cast<uint32_t>(size)};
@@ -317,11 +324,17 @@ struct QasmCircuit {
           if (qit == qregs.end() || qidx >= 0) {
             throw std::invalid_argument("bad measure: '" + std::string(b, e) + "'");
           }
+          if (qit->second.size > cit->second.size) {
+            throw std::invalid_argument("bad measure: '" + std::string(b, e) + "'");
+          }
           for (uint32_t k = 0; k < qit->second.size; ++k) {
             measQubit.push_back(qit->second.first + k);
             measClbit.push_back(cit->second.first + k);
           }
         } else {
+          if (cidx >= static_cast<long>(cit->second.size)) {
+            throw std::invalid_argument("bad measure: '" + std::string(b, e) + "'");
+          }
           measQubit.push_back(static_cast<uint32_t>(qubitOf(w, arrow)));
           measClbit.push_back(cit->second.first + static_cast<uint32_t>(cidx));
         }

@@ -401,3 +401,41 @@ def test_circuit_batch_from_qasm_files_equals_the_python_path():
             assert a[0] == b[0] and a[1] == b[1], p
             for x, y in zip(a[2:], b[2:]):
                 assert np.array_equal(x, y), p
+
+
+def test_native_qasm_reader_survives_malformed_input():
+    """The reader takes user text through the C ABI: whatever it is given, it
+    answers with a status (mutations of a valid file, truncations, junk)."""
+    from qmap_b200 import circuit as qc
+    L = _abi.load()
+    base = open(os.path.join(parity.CIRCUITS, "3_17_13.qasm")).read()
+    rng = np.random.default_rng(7)
+    junk = list("[](),;->.0123456789 piqregcxmeasurebarrier\n\t*/+-eE\"")
+    n_ok = n_err = 0
+    texts = [base[:k] for k in range(0, len(base), 7)]
+    for _ in range(1500):
+        t = list(base)
+        for _ in range(int(rng.integers(1, 6))):
+            op = int(rng.integers(0, 3))
+            pos = int(rng.integers(0, len(t)))
+            if op == 0:
+                t[pos] = junk[int(rng.integers(0, len(junk)))]
+            elif op == 1:
+                del t[pos]
+            else:
+                t.insert(pos, junk[int(rng.integers(0, len(junk)))])
+        texts.append("".join(t))
+    texts += ["qreg q[3]; cx q[0],q[7];", "qreg q[2]; creg c[1]; measure q[1] -> c[5];",
+              "qreg q[99999999999999999999];", "qreg q[2]; creg c[1]; measure q -> c;",
+              "qreg q[20000000]; qreg r[20000000];", "qreg q[2]; rz(((((((1))))))) q[0];",
+              "qreg q[2]; rz(1e999) q[0];", "qreg q[1]; u3(1,2,3,4) q[0];", ";;;;", "(", "qreg", "measure ->"]
+    for text in texts:
+        try:
+            n = qc.NativeQasm(L, text=text)
+            n.mapper_view(5)
+            n.gates()
+            n.measurements()
+            n_ok += 1
+        except _abi.QmapError:
+            n_err += 1
+    assert n_ok > 50 and n_err > 500
