@@ -439,3 +439,30 @@ def test_native_qasm_reader_survives_malformed_input():
         except _abi.QmapError:
             n_err += 1
     assert n_ok > 50 and n_err > 500
+
+
+def test_c_example_compiles_against_the_header_and_library(tmp_path):
+    """examples/route_qasm.c: include/qmap_b200.h is plain C11 (-pedantic), the
+    example links against libqmap_b200.so and runs the host part of the path
+    (QASM reader, mapper view, createLayers); without a GPU it stops at the
+    device check with exit code 3 - there is no CPU fallback."""
+    import shutil
+    import subprocess
+    import torch
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    libdir = os.path.join(ROOT, "mqt-qmap_b200", "csrc")
+    exe = str(tmp_path / "route_qasm")
+    subprocess.check_call([cc, "-std=c11", "-Wall", "-Wextra", "-pedantic", "-Werror",
+                           "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "route_qasm.c"),
+                           "-L" + libdir, "-lqmap_b200", "-Wl,-rpath," + libdir, "-o", exe])
+    r = subprocess.run([exe, os.path.join(parity.CIRCUITS, "3_17_13.qasm"),
+                        os.path.join(parity.ARCHS, "ibm_qx4.arch")], capture_output=True, text=True, timeout=120)
+    if torch.cuda.is_available():
+        assert r.returncode == 0 and "SWAP" in r.stdout, r.stderr
+    else:
+        assert r.returncode == 3 and "no CUDA device" in r.stderr, (r.returncode, r.stderr)
+    bad = subprocess.run([exe, os.path.join(parity.ARCHS, "ibm_qx4.arch"),
+                          os.path.join(parity.ARCHS, "ibm_qx4.arch")], capture_output=True, text=True, timeout=120)
+    assert bad.returncode == 1 and "reading the circuit" in bad.stderr
